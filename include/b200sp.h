@@ -1,0 +1,220 @@
+/*
+ * b200sp.h -- C ABI of libb200sp.so, the B200-native (sm_100a) CSR SpGEMM / SpMV engine.
+ *
+ * This header is the drop-in boundary for the one hot path BASELINE.json:north_star
+ * names.  Every entry point states which call of the reference (wjustin784/spMM,
+ * paths relative to the reference root) it takes the place of.  Plain pointers and
+ * sizes only: no torch / CuPy types cross this boundary.
+ *
+ * Conventions
+ *   - every function returns an int status: 0 = OK, negative = error; the text of
+ *     the last error of a handle is b200sp_last_error(handle).  The library never
+ *     calls exit() (the reference drivers do: cupy_cusparse/spgemm_from_txt_alg1.cu:12-17).
+ *   - CSR is base-0, int32 indptr/indices, fp32 or fp64 values, rows sorted by column
+ *     and duplicate free on input ("canonical", the precondition asserted at
+ *     modify_src/cupy-src/cupyx/cusparse.py:2030-2031).  Output C is canonical too.
+ *   - pointers named d* are DEVICE pointers on the handle's device, h* are HOST pointers.
+ *   - A and B may alias (every reference profiler computes A @ A).
+ *   - one handle per host thread / device; no global mutable state.
+ *   - all work is enqueued on the handle's stream (default: the legacy default
+ *     stream, like the reference: SpGEMM_alg_comparison/profiler.py:104-105).
+ */
+#ifndef B200SP_H_
+#define B200SP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200SP_VERSION 100 /* 0.1.0 */
+
+typedef struct b200sp_context *b200sp_handle_t;
+
+enum b200sp_status {
+  B200SP_OK = 0,
+  B200SP_ERR_INVALID = -1,  /* bad argument / shape / non-canonical input detected */
+  B200SP_ERR_CUDA = -2,     /* a CUDA runtime call failed */
+  B200SP_ERR_ALLOC = -3,    /* out of device or host memory (Python shim raises MemoryError) */
+  B200SP_ERR_OVERFLOW = -4, /* nnz(C) or a per-row count does not fit int32 indptr */
+  B200SP_ERR_STATE = -5,    /* numeric called without a matching symbolic */
+  B200SP_ERR_IO = -6        /* txt-CSR file could not be read / written */
+};
+
+/* value type; mirrors CUDA_R_32F / CUDA_R_64F passed at spgemm_from_txt_alg1.cu:165
+ * and cupy _dtype.to_cuda_dtype at cusparse.py:2050 */
+enum b200sp_dtype { B200SP_R_32F = 0, B200SP_R_64F = 1 };
+
+/* algorithm selector; mirrors CUSPARSE_SPGEMM_DEFAULT / ALG1 / ALG2 / ALG3 as mapped at
+ * cusparse.py:2052-2057 (alg==3 -> ALG3, alg==2 -> ALG2, anything else -> DEFAULT). */
+enum b200sp_alg { B200SP_ALG_DEFAULT = 0, B200SP_ALG1 = 1, B200SP_ALG2 = 2, B200SP_ALG3 = 3 };
+
+/* ---------------------------------------------------------------- handle ---- */
+
+int b200sp_version(void);
+
+/* replaces cusparseCreate (spgemm_from_txt_alg1.cu:144) / device.get_cusparse_handle
+ * (cusparse.py:2041).  device < 0 = current device. */
+int b200sp_create(b200sp_handle_t *handle, int device);
+/* replaces cusparseDestroy (spgemm_from_txt_alg1.cu:206); frees the workspace arena. */
+int b200sp_destroy(b200sp_handle_t handle);
+/* cudaStream_t passed as void*; NULL = legacy default stream. */
+int b200sp_set_stream(b200sp_handle_t handle, void *cuda_stream);
+/* Optional: route workspace allocations through the caller (the reference routes all
+ * temporaries through the current CuPy allocator so its peak-VRAM sampler sees them:
+ * SpGEMM_alg_comparison/profiler.py:97-98).  alloc returns a device pointer or NULL. */
+int b200sp_set_allocator(b200sp_handle_t handle, void *(*alloc_fn)(size_t bytes, void *ctx),
+                         void (*free_fn)(void *ptr, void *ctx), void *ctx);
+/* Drop the cached workspace arena (the analogue of pool.free_all_blocks(),
+ * SpGEMM_alg_comparison/profiler.py:129). */
+int b200sp_release_workspace(b200sp_handle_t handle);
+const char *b200sp_last_error(b200sp_handle_t handle);
+const char *b200sp_status_string(int status);
+
+/* ---------------------------------------------------------------- SpGEMM ---- */
+
+/*
+ * Symbolic phase of C = alpha * A @ B  (A: m x k, B: k x n, C: m x n).
+ *
+ * Replaces, in one call: cusparseSpGEMM_workEstimation x2 (spgemm_from_txt_alg1.cu:171-175,
+ * cusparse.py:2061-2068), cusparseSpGEMM_getNumProducts (spgemm_from_txt_alg3.cu:190-191),
+ * cusparseSpGEMM_estimateMemory x2 (spgemm_from_txt_alg3.cu:195-201, cusparse.py:2095-2105),
+ * the structure half of cusparseSpGEMM_compute (alg1.cu:177-181) and cusparseSpMatGetSize
+ * (alg1.cu:183).  It counts intermediate products per row, bins rows by size, computes the
+ * exact nnz of every row of C and writes the final C.indptr into dCp (m+1 int32, device,
+ * caller owned - allocated before the call exactly like alg1.cu:156 / cusparse.py:2039).
+ *
+ *   alg, chunk_fraction : B200SP_ALG1 / DEFAULT = single pass over all rows;
+ *       ALG2 / ALG3 = memory bounded mode: rows are processed in chunks that each hold at
+ *       most chunk_fraction of the intermediate products, so the spill workspace is bounded
+ *       (chunk_fraction in (0,1], default 0.2 as in spgemm_from_txt_alg3.cu:103).
+ *   num_products (host, out, may be NULL): sum_i sum_{k in A_i} nnz(B_k)  (FLOPs / 2).
+ *   nnzA, nnzB: stored entries of A and B (what cusparseCreateCsr is given, alg1.cu:149-154).
+ *   nnzC (host, out): number of stored entries of C.  One host synchronisation happens here,
+ *       as in the reference (cusparse.py:2120-2127).
+ *
+ * The handle keeps the plan (row bins, borrowed dAp/dAj/dBp/dBj/dCp pointers) for numeric.
+ */
+int b200sp_spgemm_symbolic(b200sp_handle_t handle, int64_t m, int64_t k, int64_t n, int64_t nnzA,
+                           int64_t nnzB, const int32_t *dAp, const int32_t *dAj,
+                           const int32_t *dBp, const int32_t *dBj, int alg, float chunk_fraction,
+                           int64_t *num_products, int64_t *nnzC, int32_t *dCp);
+
+/*
+ * Numeric phase: fills dCj (nnzC int32) and dCx (nnzC values), both caller owned, allocated
+ * after reading nnzC exactly like cusparse.py:2128-2131 / alg1.cu:184-186.
+ * Replaces the value half of cusparseSpGEMM_compute and cusparseSpGEMM_copy (alg1.cu:187-188,
+ * cusparse.py:2134-2137).  alpha is a HOST pointer to one value of `dtype`
+ * (CUSPARSE_POINTER_MODE_HOST, alg1.cu:145); NULL means 1.  beta is fixed at 0 as in the
+ * reference.  Columns within each row come out sorted; every column's sum is accumulated in
+ * A-row storage order with a separate multiply and add (no FMA), which is bit-for-bit what
+ * scipy.sparse's csr_matmat produces (SpGEMM_vs_SpMV/profiler.py:408) and is run-to-run
+ * deterministic (deterministic/test_deterministic.sh).
+ * May be called repeatedly with new values for the same structure.
+ */
+int b200sp_spgemm_numeric(b200sp_handle_t handle, int dtype, const void *alpha, const void *dAx,
+                          const void *dBx, int32_t *dCj, void *dCx);
+
+/*
+ * Host-buffer one-shot: H2D of A and B, symbolic, numeric, D2H of C.  This is the whole body
+ * of the reference driver between read_csr_txt_prefix and write_csr_txt_prefix
+ * (spgemm_from_txt_alg1.cu:130-195) and of the profilers' timed closure
+ * `to_gpu_sparse(A); to_gpu_sparse(B); cusparse.spgemm(...)` (SpGEMM_alg_comparison/profiler.py:210-213)
+ * plus the .get().  The output arrays live in pinned host memory OWNED BY THE HANDLE: they stay
+ * valid until the next *_host call on this handle or b200sp_destroy (do not free them).
+ * hA* == hB* (aliasing) uploads the matrix once.
+ */
+int b200sp_spgemm_host(b200sp_handle_t handle, int dtype, int64_t m, int64_t k, int64_t n,
+                       const int32_t *hAp, const int32_t *hAj, const void *hAx, const int32_t *hBp,
+                       const int32_t *hBj, const void *hBx, int alg, float chunk_fraction,
+                       const void *alpha, int32_t **hCp, int32_t **hCj, void **hCx, int64_t *nnzC,
+                       int64_t *num_products);
+/* releases arrays returned by b200sp_read_csr_txt */
+int b200sp_free_host(void *ptr);
+
+/* ------------------------------------------------------------ SpMV / SpMM ---- */
+
+/*
+ * y = alpha * A @ x + beta * y, A CSR m x n.  Replaces cusparseSpMV_bufferSize + cusparseSpMV
+ * (cusparse.py:1430-1435).  alpha / beta are HOST pointers to one value of `dtype` (NULL = 1 / 0).
+ * When *beta == 0, y is write-only (never read), as with cuSPARSE.
+ */
+int b200sp_spmv(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t nnz,
+                const int32_t *dAp, const int32_t *dAj, const void *dAx, const void *dx, void *dy,
+                const void *alpha, const void *beta);
+
+/*
+ * C = alpha * A @ B + beta * C with dense column-major B (n x ncols, leading dimension ldb) and
+ * C (m x ncols, ldc).  Replaces cusparseSpMM_bufferSize + cusparseSpMM (cusparse.py:1505-1511);
+ * with ncols == 1 this is the path `A_gpu @ x_gpu` with an (n,1) vector takes in the reference
+ * (cupyx/scipy/sparse/_csr.py:217-225, SpGEMM_vs_SpMV/profiler.py:490-493).
+ */
+int b200sp_spmm(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t nnz,
+                int64_t ncols, const int32_t *dAp, const int32_t *dAj, const void *dAx,
+                const void *dB, int64_t ldb, void *dC, int64_t ldc, const void *alpha,
+                const void *beta);
+
+/* Host-buffer one-shot SpMV (H2D of A and x, kernel, D2H of y): the profilers' timed closure
+ * `to_gpu_sparse(A); cp.asarray(C); A_gpu @ C_gpu` (SpGEMM_vs_SpMV/profiler.py:490-493). */
+int b200sp_spmv_host(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t nnz,
+                     const int32_t *hAp, const int32_t *hAj, const void *hAx, const void *hx,
+                     void *hy, const void *alpha, const void *beta);
+
+/* -------------------------------------------------- canonical-format helpers ---- */
+
+/* 1 in *result when every row of the CSR has strictly increasing column indices (sorted, no
+ * duplicates) and all indices are in [0, ncols).  Replaces the canonical-format elementwise
+ * kernel + .all() (cupyx/scipy/sparse/_compressed.py:177-192) behind has_canonical_format. */
+int b200sp_csr_is_canonical(b200sp_handle_t handle, int64_t m, int64_t ncols, const int32_t *dAp,
+                            const int32_t *dAj, int *result);
+
+/* In-row column sort of a CSR (values follow their columns).  Replaces cusparseXcsrsort +
+ * gather used by csr_matrix.sort_indices() (cupyx/cusparse.py:832-866). */
+int b200sp_csr_sort_indices(b200sp_handle_t handle, int dtype, int64_t m, int64_t nnz,
+                            const int32_t *dAp, int32_t *dAj, void *dAx);
+
+/* ----------------------------------------------------------- statistics ---- */
+
+#define B200SP_MAX_BINS 16
+
+typedef struct b200sp_stats {
+  int64_t num_products;       /* of the last symbolic */
+  int64_t nnz_c;              /* of the last symbolic */
+  int64_t workspace_bytes;    /* arena currently held by the handle */
+  int64_t peak_workspace_bytes; /* high-water mark of the arena since create / reset */
+  int64_t max_row_products;   /* largest per-row intermediate-product count */
+  int32_t num_chunks;         /* row chunks used by the last symbolic (1 unless ALG2/ALG3) */
+  int32_t num_bins;
+  int64_t sym_bin_rows[B200SP_MAX_BINS]; /* rows per symbolic bin (by product upper bound) */
+  int64_t num_bin_rows[B200SP_MAX_BINS]; /* rows per numeric bin (by exact nnz of the C row) */
+  int64_t kernel_launches;    /* kernels launched by this handle since create / reset */
+  float ms_symbolic;          /* device time of the last symbolic / numeric (CUDA events) */
+  float ms_numeric;
+} b200sp_stats;
+
+int b200sp_get_stats(b200sp_handle_t handle, b200sp_stats *stats);
+int b200sp_reset_stats(b200sp_handle_t handle);
+
+/* ------------------------------------------------------------- txt-CSR I/O ---- */
+
+/*
+ * The reference's on-disk format: <prefix>_indptr.txt, <prefix>_indices.txt, <prefix>_data.txt,
+ * one number per line (np.savetxt "%d" / "%.9g", cupy_cusparse/gen_and_save_alg1_txt.py:12-14).
+ * Reader replaces read_csr_txt_prefix (spgemm_from_txt_alg1.cu:19-34,52-70): integers parsed as
+ * long long then narrowed to int32, values parsed as double then narrowed to float.  rows =
+ * len(indptr)-1, nnz = len(indices); the column count is not stored in the format.
+ * Arrays are malloc'ed by the library; release with b200sp_free_host.
+ */
+int b200sp_read_csr_txt(const char *prefix, int64_t *rows, int64_t *nnz, int32_t **hp, int32_t **hj,
+                        float **hx, char *errbuf, size_t errbuf_len);
+/* Writer replaces write_csr_txt_prefix (spgemm_from_txt_alg1.cu:35-46,72-76): values printed
+ * with 9 significant digits in the default (%g-like) float format, which round-trips fp32. */
+int b200sp_write_csr_txt(const char *prefix, int64_t rows, int64_t nnz, const int32_t *hp,
+                         const int32_t *hj, const float *hx, char *errbuf, size_t errbuf_len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SP_H_ */

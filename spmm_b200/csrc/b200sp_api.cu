@@ -1,0 +1,786 @@
+// b200sp_api.cu -- C ABI of libb200sp.so (see include/b200sp.h) and host orchestration.
+//
+// Host side of the hot path: owns the workspace arena (with a high-water mark, the analogue of
+// the CuPy MemoryPool the reference samples: SpGEMM_alg_comparison/profiler.py:82-143), plans
+// the bins, launches the sm_100a kernels and performs the two host synchronisations the
+// algorithm needs (bin sizes after the product count; nnz(C) after the symbolic pass - the
+// latter is the same sync the reference has at cupyx/cusparse.py:2120-2127).
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <cmath>
+#include <string>
+#include <vector>
+
+#include "../../include/b200sp.h"
+#include "spgemm_numeric.cuh"
+#include "spgemm_setup.cuh"
+#include "spgemm_symbolic.cuh"
+#include "spmv.cuh"
+#include "csr_utils.cuh"
+
+using namespace b200sp;
+
+namespace {
+
+constexpr size_t SMEM_MAX = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100
+constexpr size_t SMEM_BITMAP_MAX = 200 * 1024;  // budget for an n-bit bitmap in shared memory
+
+struct Buffer {  // grow-only device buffer
+  void *ptr = nullptr;
+  size_t size = 0;
+};
+
+enum SymKind { SYM_GROUP8, SYM_WARP, SYM_CTA_HASH, SYM_CTA_BITMAP };
+enum NumKind { NUM_GROUP8, NUM_WARP, NUM_CTA_HASH, NUM_GLOBAL };
+
+struct BinPlan {
+  int kind;
+  int S;  // table slots (hash kinds)
+};
+
+struct Plan {
+  bool valid = false;
+  int m = 0, k = 0, n = 0;
+  int64_t nnzA = 0, nnzB = 0;
+  const int *Ap = nullptr, *Aj = nullptr, *Bp = nullptr, *Bj = nullptr;
+  int *Cp = nullptr;
+  int alg = 0;
+  int num_chunks = 1;
+  BinLimits sym_limits{}, num_limits{};
+  BinPlan sym_bins[MAX_BINS]{}, num_bins[MAX_BINS]{};
+  int sym_count[MAX_BINS]{}, num_count[MAX_BINS]{};
+  int *rows_sym = nullptr, *rows_num = nullptr;  // device, inside ws
+  int64_t num_products = 0, nnzC = 0, max_row_products = 0;
+};
+
+}  // namespace
+
+struct b200sp_context {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  void *(*alloc_fn)(size_t, void *) = nullptr;
+  void (*free_fn)(void *, void *) = nullptr;
+  void *alloc_ctx = nullptr;
+  Buffer ws;       // plan workspace (row lists, counters, scan tiles)
+  Buffer ws2;      // global bitmap workspace of the heavy-row kernels
+  Buffer io[10];   // device staging of the *_host entry points
+  void *pinned_out[3] = {nullptr, nullptr, nullptr};  // host staging of C (handle owned)
+  size_t pinned_out_size[3] = {0, 0, 0};
+  Counters *h_counters = nullptr;  // pinned
+  int64_t bytes_live = 0, bytes_peak = 0;
+  int64_t launches = 0;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  float ms_symbolic = 0.f, ms_numeric = 0.f;
+  bool numeric_timed = false;
+  Plan plan;
+  std::string err;
+};
+
+namespace {
+
+int fail(b200sp_context *h, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (h) h->err = buf;
+  return code;
+}
+
+#define CUDA_TRY(h, expr)                                                                    \
+  do {                                                                                       \
+    cudaError_t e_ = (expr);                                                                 \
+    if (e_ != cudaSuccess) {                                                                 \
+      int code_ = (e_ == cudaErrorMemoryAllocation) ? B200SP_ERR_ALLOC : B200SP_ERR_CUDA;    \
+      return fail(h, code_, "CUDA error %s:%d: %s (%s)", __FILE__, __LINE__,                 \
+                  cudaGetErrorString(e_), #expr);                                            \
+    }                                                                                        \
+  } while (0)
+
+#define TRY(expr)              \
+  do {                         \
+    int rc_ = (expr);          \
+    if (rc_ != B200SP_OK) return rc_; \
+  } while (0)
+
+int dev_alloc(b200sp_context *h, void **p, size_t bytes) {
+  *p = nullptr;
+  if (bytes == 0) return B200SP_OK;
+  if (h->alloc_fn) {
+    *p = h->alloc_fn(bytes, h->alloc_ctx);
+    if (!*p) return fail(h, B200SP_ERR_ALLOC, "caller allocator returned NULL for %zu bytes", bytes);
+  } else {
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(h, B200SP_ERR_ALLOC, "out of device memory allocating %zu bytes: %s", bytes,
+                  cudaGetErrorString(e));
+    }
+  }
+  h->bytes_live += (int64_t)bytes;
+  h->bytes_peak = std::max(h->bytes_peak, h->bytes_live);
+  return B200SP_OK;
+}
+
+void dev_free(b200sp_context *h, void *p, size_t bytes) {
+  if (!p) return;
+  if (h->free_fn) h->free_fn(p, h->alloc_ctx);
+  else cudaFree(p);
+  h->bytes_live -= (int64_t)bytes;
+}
+
+// Grow-only: contents are NOT preserved across a grow.
+int ensure(b200sp_context *h, Buffer &b, size_t bytes) {
+  if (bytes <= b.size) return B200SP_OK;
+  if (b.ptr) {
+    cudaStreamSynchronize(h->stream);
+    dev_free(h, b.ptr, b.size);
+    b.ptr = nullptr;
+    b.size = 0;
+  }
+  const size_t want = (bytes + 255) & ~(size_t)255;
+  TRY(dev_alloc(h, &b.ptr, want));
+  b.size = want;
+  return B200SP_OK;
+}
+
+void release(b200sp_context *h, Buffer &b) {
+  if (b.ptr) dev_free(h, b.ptr, b.size);
+  b.ptr = nullptr;
+  b.size = 0;
+}
+
+template <typename K>
+int set_smem(b200sp_context *h, K kernel, size_t bytes) {
+  if (bytes > 48 * 1024) {
+    CUDA_TRY(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  }
+  return B200SP_OK;
+}
+
+int check_launch(b200sp_context *h, const char *what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(h, B200SP_ERR_CUDA, "launch of %s failed: %s", what, cudaGetErrorString(e));
+  h->launches++;
+  return B200SP_OK;
+}
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+// =============================================================================== handle ====
+
+extern "C" int b200sp_version(void) { return B200SP_VERSION; }
+
+extern "C" const char *b200sp_status_string(int status) {
+  switch (status) {
+    case B200SP_OK: return "ok";
+    case B200SP_ERR_INVALID: return "invalid argument";
+    case B200SP_ERR_CUDA: return "CUDA error";
+    case B200SP_ERR_ALLOC: return "out of memory";
+    case B200SP_ERR_OVERFLOW: return "int32 overflow";
+    case B200SP_ERR_STATE: return "bad call sequence";
+    case B200SP_ERR_IO: return "I/O error";
+    default: return "unknown status";
+  }
+}
+
+extern "C" int b200sp_create(b200sp_handle_t *handle, int device) {
+  if (!handle) return B200SP_ERR_INVALID;
+  *handle = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return B200SP_ERR_CUDA;  // no CPU fallback: the product needs a CUDA device
+  }
+  b200sp_context *h = new (std::nothrow) b200sp_context();
+  if (!h) return B200SP_ERR_ALLOC;
+  if (device < 0) {
+    if (cudaGetDevice(&device) != cudaSuccess) device = 0;
+  }
+  h->device = device;
+  if (cudaSetDevice(device) != cudaSuccess ||
+      cudaMallocHost((void **)&h->h_counters, sizeof(Counters)) != cudaSuccess) {
+    cudaGetLastError();
+    delete h;
+    return B200SP_ERR_CUDA;
+  }
+  for (auto &e : h->ev) cudaEventCreate(&e);
+  *handle = h;
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_release_workspace(b200sp_handle_t h) {
+  if (!h) return B200SP_ERR_INVALID;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  release(h, h->ws);
+  release(h, h->ws2);
+  for (auto &b : h->io) release(h, b);
+  h->plan.valid = false;
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_destroy(b200sp_handle_t h) {
+  if (!h) return B200SP_OK;
+  b200sp_release_workspace(h);
+  for (int i = 0; i < 3; ++i)
+    if (h->pinned_out[i]) cudaFreeHost(h->pinned_out[i]);
+  if (h->h_counters) cudaFreeHost(h->h_counters);
+  for (auto &e : h->ev)
+    if (e) cudaEventDestroy(e);
+  delete h;
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_set_stream(b200sp_handle_t h, void *cuda_stream) {
+  if (!h) return B200SP_ERR_INVALID;
+  h->stream = (cudaStream_t)cuda_stream;
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_set_allocator(b200sp_handle_t h, void *(*alloc_fn)(size_t, void *),
+                                    void (*free_fn)(void *, void *), void *ctx) {
+  if (!h || ((alloc_fn == nullptr) != (free_fn == nullptr))) return B200SP_ERR_INVALID;
+  b200sp_release_workspace(h);  // buffers must be freed by the allocator that made them
+  h->alloc_fn = alloc_fn;
+  h->free_fn = free_fn;
+  h->alloc_ctx = ctx;
+  return B200SP_OK;
+}
+
+extern "C" const char *b200sp_last_error(b200sp_handle_t h) { return h ? h->err.c_str() : "null handle"; }
+
+extern "C" int b200sp_get_stats(b200sp_handle_t h, b200sp_stats *s) {
+  if (!h || !s) return B200SP_ERR_INVALID;
+  memset(s, 0, sizeof *s);
+  if (h->numeric_timed) {
+    cudaEventSynchronize(h->ev[3]);
+    cudaEventElapsedTime(&h->ms_numeric, h->ev[2], h->ev[3]);
+  }
+  const Plan &p = h->plan;
+  s->num_products = p.num_products;
+  s->nnz_c = p.nnzC;
+  s->workspace_bytes = h->bytes_live;
+  s->peak_workspace_bytes = h->bytes_peak;
+  s->max_row_products = p.max_row_products;
+  s->num_chunks = p.num_chunks;
+  s->num_bins = p.sym_limits.nbins;
+  for (int b = 0; b < MAX_BINS; ++b) {
+    s->sym_bin_rows[b] = p.sym_count[b];
+    s->num_bin_rows[b] = p.num_count[b];
+  }
+  s->kernel_launches = h->launches;
+  s->ms_symbolic = h->ms_symbolic;
+  s->ms_numeric = h->ms_numeric;
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_reset_stats(b200sp_handle_t h) {
+  if (!h) return B200SP_ERR_INVALID;
+  h->bytes_peak = h->bytes_live;
+  h->launches = 0;
+  return B200SP_OK;
+}
+
+// =============================================================================== SpGEMM ====
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+void plan_bins(Plan &p) {
+  const size_t bitmap_bytes = (size_t)((p.n + 31) / 32) * 4;
+  // symbolic bins, by the upper bound ub = min(products, n) of nnz(C_i)
+  const int sl[6] = {32, 128, 512, 4096, 16384, INT_MAX};
+  p.sym_limits.nbins = 6;
+  for (int b = 0; b < 6; ++b) p.sym_limits.limit[b] = sl[b];
+  p.sym_bins[0] = {SYM_GROUP8, 64};
+  p.sym_bins[1] = {SYM_WARP, 256};
+  p.sym_bins[2] = {SYM_WARP, 1024};
+  p.sym_bins[3] = {bitmap_bytes <= 8192 * 4 ? SYM_CTA_BITMAP : SYM_CTA_HASH, 8192};
+  p.sym_bins[4] = {bitmap_bytes <= 32768 * 4 ? SYM_CTA_BITMAP : SYM_CTA_HASH, 32768};
+  p.sym_bins[5] = {SYM_CTA_BITMAP, 0};
+  // numeric bins, by the exact nnz(C_i)
+  const int nl[6] = {32, 128, 512, 6144, 12288, INT_MAX};
+  p.num_limits.nbins = 6;
+  for (int b = 0; b < 6; ++b) p.num_limits.limit[b] = nl[b];
+  p.num_bins[0] = {NUM_GROUP8, 64};
+  p.num_bins[1] = {NUM_WARP, 256};
+  p.num_bins[2] = {NUM_WARP, 1024};
+  p.num_bins[3] = {NUM_CTA_HASH, 8192};
+  p.num_bins[4] = {NUM_CTA_HASH, 16384};
+  p.num_bins[5] = {NUM_GLOBAL, 0};
+}
+
+int persistent_grid(int nrows, size_t smem_bytes) {
+  int per_sm = smem_bytes ? (int)std::min<size_t>(8, SMEM_MAX / std::max<size_t>(smem_bytes, 1)) : 8;
+  per_sm = std::max(per_sm, 1);
+  return std::max(1, std::min(nrows, NUM_SMS * per_sm));
+}
+
+int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
+  Plan &p = h->plan;
+  const BinPlan &bp = p.sym_bins[b];
+  cudaStream_t st = h->stream;
+  switch (bp.kind) {
+    case SYM_GROUP8: {
+      const size_t smem = 16 * (size_t)bp.S * 4;
+      k_sym_hash_group<8><<<(cnt + 15) / 16, 128, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp);
+      return check_launch(h, "k_sym_hash_group<8>");
+    }
+    case SYM_WARP: {
+      const size_t smem = 4 * (size_t)bp.S * 4;
+      k_sym_hash_group<32><<<(cnt + 3) / 4, 128, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp);
+      return check_launch(h, "k_sym_hash_group<32>");
+    }
+    case SYM_CTA_HASH: {
+      const size_t smem = (size_t)bp.S * 4;
+      TRY(set_smem(h, k_sym_hash_cta, smem));
+      k_sym_hash_cta<<<persistent_grid(cnt, smem), 256, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp);
+      return check_launch(h, "k_sym_hash_cta");
+    }
+    case SYM_CTA_BITMAP: {
+      const size_t bytes = (size_t)((p.n + 31) / 32) * 4;
+      if (bytes <= SMEM_BITMAP_MAX) {
+        TRY(set_smem(h, k_sym_bitmap_cta<true>, bytes));
+        k_sym_bitmap_cta<true><<<persistent_grid(cnt, bytes + 64), 256, bytes, st>>>(
+            rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp, nullptr);
+        return check_launch(h, "k_sym_bitmap_cta<smem>");
+      }
+      int grid = std::max(1, std::min(cnt, 2 * NUM_SMS / p.num_chunks));
+      TRY(ensure(h, h->ws2, (size_t)grid * bytes));
+      CUDA_TRY(h, cudaMemsetAsync(h->ws2.ptr, 0, (size_t)grid * bytes, st));
+      k_sym_bitmap_cta<false><<<grid, 256, 0, st>>>(rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp,
+                                                    (unsigned *)h->ws2.ptr);
+      return check_launch(h, "k_sym_bitmap_cta<global>");
+    }
+  }
+  return fail(h, B200SP_ERR_INVALID, "bad symbolic bin kind");
+}
+
+template <typename T>
+int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alpha, const T *Ax,
+                       const T *Bx, int *Cj, T *Cx) {
+  Plan &p = h->plan;
+  const BinPlan &bp = p.num_bins[b];
+  cudaStream_t st = h->stream;
+  switch (bp.kind) {
+    case NUM_GROUP8: {
+      const size_t smem = 16 * (size_t)bp.S * (sizeof(T) + 4);
+      k_num_hash_group<8, T><<<(cnt + 15) / 16, 128, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+      return check_launch(h, "k_num_hash_group<8>");
+    }
+    case NUM_WARP: {
+      const size_t smem = 4 * (size_t)bp.S * (sizeof(T) + 4);
+      TRY(set_smem(h, k_num_hash_group<32, T>, smem));
+      k_num_hash_group<32, T><<<(cnt + 3) / 4, 128, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+      return check_launch(h, "k_num_hash_group<32>");
+    }
+    case NUM_CTA_HASH: {
+      const size_t smem = (size_t)bp.S * (sizeof(T) + 4);
+      TRY(set_smem(h, k_num_hash_cta<T>, smem));
+      k_num_hash_cta<T><<<persistent_grid(cnt, smem + 2304), 256, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+      return check_launch(h, "k_num_hash_cta");
+    }
+    case NUM_GLOBAL: {
+      const size_t bytes = (size_t)((p.n + 31) / 32) * 8;  // bitmap + prefix
+      int grid = std::max(1, std::min(cnt, 2 * NUM_SMS / p.num_chunks));
+      TRY(ensure(h, h->ws2, (size_t)grid * bytes));
+      CUDA_TRY(h, cudaMemsetAsync(h->ws2.ptr, 0, (size_t)grid * bytes, st));
+      k_num_bitmap_global<T><<<grid, 256, 0, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha, (unsigned *)h->ws2.ptr);
+      return check_launch(h, "k_num_bitmap_global");
+    }
+  }
+  return fail(h, B200SP_ERR_INVALID, "bad numeric bin kind");
+}
+
+template <typename T>
+int run_numeric(b200sp_context *h, const void *alpha, const void *Ax, const void *Bx, int *Cj, void *Cx) {
+  Plan &p = h->plan;
+  const T a = alpha ? *(const T *)alpha : T(1);
+  int off = 0;
+  for (int b = 0; b < p.num_limits.nbins; ++b) {
+    const int cnt = p.num_count[b];
+    for (int c = 0; c < p.num_chunks && cnt > 0; ++c) {
+      const int r0 = (int)((int64_t)cnt * c / p.num_chunks), r1 = (int)((int64_t)cnt * (c + 1) / p.num_chunks);
+      if (r1 > r0) TRY(launch_numeric_bin<T>(h, b, p.rows_num + off + r0, r1 - r0, a, (const T *)Ax, (const T *)Bx, Cj, (T *)Cx));
+    }
+    off += cnt;
+  }
+  return B200SP_OK;
+}
+
+}  // namespace
+
+extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, int64_t n, int64_t nnzA,
+                                      int64_t nnzB, const int32_t *dAp, const int32_t *dAj,
+                                      const int32_t *dBp, const int32_t *dBj, int alg,
+                                      float chunk_fraction, int64_t *num_products, int64_t *nnzC,
+                                      int32_t *dCp) {
+  if (!h) return B200SP_ERR_INVALID;
+  Plan &p = h->plan;
+  p.valid = false;
+  if (m < 0 || k < 0 || n < 0 || nnzA < 0 || nnzB < 0 || m >= INT32_MAX || k >= INT32_MAX || n >= INT32_MAX ||
+      nnzA > INT32_MAX || nnzB > INT32_MAX)
+    return fail(h, B200SP_ERR_INVALID, "bad shape m=%lld k=%lld n=%lld nnzA=%lld nnzB=%lld", (long long)m,
+                (long long)k, (long long)n, (long long)nnzA, (long long)nnzB);
+  if (!dAp || !dBp || !dCp || !nnzC || (nnzA && !dAj) || (nnzB && !dBj))
+    return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  const bool chunked = (alg == B200SP_ALG2 || alg == B200SP_ALG3);
+  if (chunked && !(chunk_fraction > 0.f && chunk_fraction <= 1.f))
+    return fail(h, B200SP_ERR_INVALID, "chunk_fraction must be in (0,1], got %f", chunk_fraction);
+  DeviceGuard guard(h->device);
+  cudaStream_t st = h->stream;
+  p.m = (int)m; p.k = (int)k; p.n = (int)n; p.nnzA = nnzA; p.nnzB = nnzB;
+  p.Ap = dAp; p.Aj = dAj; p.Bp = dBp; p.Bj = dBj; p.Cp = dCp;
+  p.alg = alg;
+  p.num_chunks = chunked ? (int)std::min<double>(64.0, std::ceil(1.0 / (double)chunk_fraction - 1e-6)) : 1;
+  p.num_products = 0; p.nnzC = 0; p.max_row_products = 0;
+  memset(p.sym_count, 0, sizeof p.sym_count);
+  memset(p.num_count, 0, sizeof p.num_count);
+  plan_bins(p);
+  h->numeric_timed = false;
+  if (num_products) *num_products = 0;
+  *nnzC = 0;
+  if (m == 0) {
+    CUDA_TRY(h, cudaMemsetAsync(dCp, 0, sizeof(int), st));
+    p.valid = true;
+    return B200SP_OK;
+  }
+  // workspace: counters | rowub | rows_sym | rows_num | scan tile sums
+  const int ntiles = (p.m + SCAN_TILE - 1) / SCAN_TILE;
+  const size_t o_ub = align_up(sizeof(Counters), 256);
+  const size_t o_rs = o_ub + align_up((size_t)p.m * 4, 256);
+  const size_t o_rn = o_rs + align_up((size_t)p.m * 4, 256);
+  const size_t o_ts = o_rn + align_up((size_t)p.m * 4, 256);
+  TRY(ensure(h, h->ws, o_ts + (size_t)ntiles * 8));
+  char *base = (char *)h->ws.ptr;
+  Counters *ctr = (Counters *)base;
+  int *rowub = (int *)(base + o_ub);
+  p.rows_sym = (int *)(base + o_rs);
+  p.rows_num = (int *)(base + o_rn);
+  long long *tile_sums = (long long *)(base + o_ts);
+
+  cudaEventRecord(h->ev[0], st);
+  CUDA_TRY(h, cudaMemsetAsync(ctr, 0, sizeof(Counters), st));
+  {
+    const double avg = (double)nnzA / (double)m;
+    const int G = avg <= 2 ? 2 : avg <= 6 ? 4 : avg <= 12 ? 8 : avg <= 24 ? 16 : 32;
+    const int grid = std::max(1, std::min((int)((m + 256 / G - 1) / (256 / G)), NUM_SMS * 8));
+    switch (G) {
+      case 2: k_row_products<2><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
+      case 4: k_row_products<4><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
+      case 8: k_row_products<8><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
+      case 16: k_row_products<16><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
+      default: k_row_products<32><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
+    }
+    TRY(check_launch(h, "k_row_products"));
+  }
+  const int sgrid = std::max(1, std::min((p.m + 255) / 256, NUM_SMS * 8));
+  k_scatter_rows<false><<<sgrid, 256, 0, st>>>(p.m, rowub, p.sym_limits, ctr, p.rows_sym);
+  TRY(check_launch(h, "k_scatter_rows<sym>"));
+  // sync #1: product total + symbolic bin sizes
+  CUDA_TRY(h, cudaMemcpyAsync(h->h_counters, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(h, cudaStreamSynchronize(st));
+  if (h->h_counters->overflow)
+    return fail(h, B200SP_ERR_OVERFLOW, "a row of A@B has more than 2^31-1 intermediate products");
+  p.num_products = (int64_t)h->h_counters->total_products;
+  p.max_row_products = h->h_counters->max_row_products;
+  if (num_products) *num_products = p.num_products;
+  int off = 0;
+  for (int b = 0; b < p.sym_limits.nbins; ++b) {
+    const int cnt = p.sym_count[b] = h->h_counters->sym_count[b];
+    for (int c = 0; c < p.num_chunks && cnt > 0; ++c) {
+      const int r0 = (int)((int64_t)cnt * c / p.num_chunks), r1 = (int)((int64_t)cnt * (c + 1) / p.num_chunks);
+      if (r1 > r0) TRY(launch_symbolic_bin(h, b, p.rows_sym + off + r0, r1 - r0));
+    }
+    off += cnt;
+  }
+  // counts -> indptr
+  if (ntiles <= 16) {
+    k_scan_single<<<1, SCAN_THREADS, 0, st>>>(dCp, p.m, ctr);
+    TRY(check_launch(h, "k_scan_single"));
+  } else {
+    k_scan_tile_sums<<<ntiles, SCAN_THREADS, 0, st>>>(dCp, p.m, tile_sums);
+    TRY(check_launch(h, "k_scan_tile_sums"));
+    k_scan_tile_offsets<<<1, SCAN_THREADS, 0, st>>>(tile_sums, ntiles, dCp, p.m, ctr);
+    TRY(check_launch(h, "k_scan_tile_offsets"));
+    k_scan_apply<<<ntiles, SCAN_THREADS, 0, st>>>(dCp, p.m, tile_sums);
+    TRY(check_launch(h, "k_scan_apply"));
+  }
+  k_hist_numeric<<<sgrid, 256, 0, st>>>(p.m, dCp, p.num_limits, ctr);
+  TRY(check_launch(h, "k_hist_numeric"));
+  k_scatter_rows<true><<<sgrid, 256, 0, st>>>(p.m, dCp, p.num_limits, ctr, p.rows_num);
+  TRY(check_launch(h, "k_scatter_rows<num>"));
+  cudaEventRecord(h->ev[1], st);
+  // sync #2: nnz(C) + numeric bin sizes (the reference's cusparseSpMatGetSize sync)
+  CUDA_TRY(h, cudaMemcpyAsync(h->h_counters, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(h, cudaStreamSynchronize(st));
+  cudaEventElapsedTime(&h->ms_symbolic, h->ev[0], h->ev[1]);
+  p.nnzC = (int64_t)h->h_counters->nnz_c;
+  for (int b = 0; b < p.num_limits.nbins; ++b) p.num_count[b] = h->h_counters->num_count[b];
+  *nnzC = p.nnzC;
+  if (p.nnzC > INT32_MAX)
+    return fail(h, B200SP_ERR_OVERFLOW, "nnz(C) = %lld does not fit the int32 indptr of CSR", (long long)p.nnzC);
+  p.valid = true;
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_spgemm_numeric(b200sp_handle_t h, int dtype, const void *alpha, const void *dAx,
+                                     const void *dBx, int32_t *dCj, void *dCx) {
+  if (!h) return B200SP_ERR_INVALID;
+  Plan &p = h->plan;
+  if (!p.valid) return fail(h, B200SP_ERR_STATE, "spgemm_numeric called without a successful spgemm_symbolic");
+  if (dtype != B200SP_R_32F && dtype != B200SP_R_64F) return fail(h, B200SP_ERR_INVALID, "unsupported dtype %d", dtype);
+  if (p.nnzC == 0) return B200SP_OK;
+  if (!dAx || !dBx || !dCj || !dCx) return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  DeviceGuard guard(h->device);
+  cudaEventRecord(h->ev[2], h->stream);
+  int rc = dtype == B200SP_R_32F ? run_numeric<float>(h, alpha, dAx, dBx, dCj, dCx)
+                                 : run_numeric<double>(h, alpha, dAx, dBx, dCj, dCx);
+  cudaEventRecord(h->ev[3], h->stream);
+  h->numeric_timed = (rc == B200SP_OK);
+  return rc;
+}
+
+// ========================================================================== SpMV / SpMM ====
+
+namespace {
+
+template <typename T>
+int run_spmv(b200sp_context *h, int m, int n, int64_t nnz, int64_t ncols, const int *Ap, const int *Aj,
+             const T *Ax, const T *X, int64_t ldx, T *Y, int64_t ldy, const void *alpha, const void *beta) {
+  (void)n;
+  const T a = alpha ? *(const T *)alpha : T(1);
+  const T b = beta ? *(const T *)beta : T(0);
+  cudaStream_t st = h->stream;
+  if (m == 0 || ncols == 0) return B200SP_OK;
+  const char *mode = getenv("B200SP_SPMV_KERNEL");  // "vector" forces the row-group kernel
+  const bool want_stream = !(mode && strcmp(mode, "vector") == 0);
+  if (want_stream && ncols == 1 && nnz > 0) {
+    const int ntiles = (int)((nnz + SPMV_TILE - 1) / SPMV_TILE);
+    const size_t o_c = align_up((size_t)ntiles * sizeof(SpmvTileInfo), 256);
+    const size_t o_t = o_c + align_up((size_t)ntiles * sizeof(T), 256);
+    TRY(ensure(h, h->ws2, o_t + (size_t)ntiles * sizeof(T)));
+    char *base = (char *)h->ws2.ptr;
+    SpmvTileInfo *info = (SpmvTileInfo *)base;
+    T *carry = (T *)(base + o_c), *tail = (T *)(base + o_t);
+    const int vec_ok = (((uintptr_t)Aj | (uintptr_t)Ax) & 15) == 0;
+    const int egrid = std::max(1, std::min((m + 255) / 256, NUM_SMS * 8));
+    k_spmv_empty_rows<T><<<egrid, 256, 0, st>>>(m, Ap, Y, b);
+    TRY(check_launch(h, "k_spmv_empty_rows"));
+    k_spmv_stream<T><<<ntiles, SPMV_THREADS, 0, st>>>(m, (int)nnz, Ap, Aj, Ax, X, Y, a, b, info, carry, tail, vec_ok);
+    TRY(check_launch(h, "k_spmv_stream"));
+    k_spmv_fixup<T><<<(ntiles + 255) / 256, 256, 0, st>>>(ntiles, info, carry, tail, Y, a, b);
+    return check_launch(h, "k_spmv_fixup");
+  }
+  const double avg = (double)nnz / (double)m;
+  const int G = avg <= 3 ? 2 : avg <= 6 ? 4 : avg <= 12 ? 8 : avg <= 24 ? 16 : 32;
+  const int gx = std::max(1, std::min((int)(((int64_t)m + 256 / G - 1) / (256 / G)), NUM_SMS * 16));
+  dim3 grid(gx, (unsigned)ncols);
+  switch (G) {
+    case 2: k_spmv_vector<2, T><<<grid, 256, 0, st>>>(m, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+    case 4: k_spmv_vector<4, T><<<grid, 256, 0, st>>>(m, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+    case 8: k_spmv_vector<8, T><<<grid, 256, 0, st>>>(m, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+    case 16: k_spmv_vector<16, T><<<grid, 256, 0, st>>>(m, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+    default: k_spmv_vector<32, T><<<grid, 256, 0, st>>>(m, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+  }
+  return check_launch(h, "k_spmv_vector");
+}
+
+}  // namespace
+
+extern "C" int b200sp_spmm(b200sp_handle_t h, int dtype, int64_t m, int64_t n, int64_t nnz, int64_t ncols,
+                           const int32_t *dAp, const int32_t *dAj, const void *dAx, const void *dB,
+                           int64_t ldb, void *dC, int64_t ldc, const void *alpha, const void *beta) {
+  if (!h) return B200SP_ERR_INVALID;
+  if (m < 0 || n < 0 || nnz < 0 || ncols < 0 || m >= INT32_MAX || n >= INT32_MAX || nnz > INT32_MAX || ncols > 65535)
+    return fail(h, B200SP_ERR_INVALID, "bad shape m=%lld n=%lld nnz=%lld ncols=%lld", (long long)m, (long long)n,
+                (long long)nnz, (long long)ncols);
+  if (dtype != B200SP_R_32F && dtype != B200SP_R_64F) return fail(h, B200SP_ERR_INVALID, "unsupported dtype %d", dtype);
+  if (m == 0 || ncols == 0) return B200SP_OK;
+  if (!dAp || !dC || (nnz && (!dAj || !dAx || !dB))) return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  if (ncols > 1 && (ldb < n || ldc < m)) return fail(h, B200SP_ERR_INVALID, "leading dimension too small");
+  DeviceGuard guard(h->device);
+  if (dtype == B200SP_R_32F)
+    return run_spmv<float>(h, (int)m, (int)n, nnz, ncols, dAp, dAj, (const float *)dAx, (const float *)dB, ldb,
+                           (float *)dC, ldc, alpha, beta);
+  return run_spmv<double>(h, (int)m, (int)n, nnz, ncols, dAp, dAj, (const double *)dAx, (const double *)dB, ldb,
+                          (double *)dC, ldc, alpha, beta);
+}
+
+extern "C" int b200sp_spmv(b200sp_handle_t h, int dtype, int64_t m, int64_t n, int64_t nnz, const int32_t *dAp,
+                           const int32_t *dAj, const void *dAx, const void *dx, void *dy, const void *alpha,
+                           const void *beta) {
+  return b200sp_spmm(h, dtype, m, n, nnz, 1, dAp, dAj, dAx, dx, n, dy, m, alpha, beta);
+}
+
+// ==================================================================== canonical helpers ====
+
+extern "C" int b200sp_csr_is_canonical(b200sp_handle_t h, int64_t m, int64_t ncols, const int32_t *dAp,
+                                       const int32_t *dAj, int *result) {
+  if (!h || !result || m < 0 || m >= INT32_MAX || ncols < 0 || ncols > INT32_MAX || !dAp)
+    return h ? fail(h, B200SP_ERR_INVALID, "bad argument") : B200SP_ERR_INVALID;
+  *result = 1;
+  if (m == 0) return B200SP_OK;
+  DeviceGuard guard(h->device);
+  TRY(ensure(h, h->ws2, 256));
+  int *flag = (int *)h->ws2.ptr;
+  CUDA_TRY(h, cudaMemsetAsync(flag, 0, sizeof(int), h->stream));
+  const int grid = std::max(1, std::min((int)((m + 7) / 8), NUM_SMS * 8));
+  k_csr_check_canonical<<<grid, 256, 0, h->stream>>>((int)m, (int)ncols, dAp, dAj, flag);
+  TRY(check_launch(h, "k_csr_check_canonical"));
+  int bad = 0;
+  CUDA_TRY(h, cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+  *result = bad ? 0 : 1;
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_csr_sort_indices(b200sp_handle_t h, int dtype, int64_t m, int64_t nnz, const int32_t *dAp,
+                                       int32_t *dAj, void *dAx) {
+  if (!h) return B200SP_ERR_INVALID;
+  if (m < 0 || m >= INT32_MAX || nnz < 0 || nnz > INT32_MAX || !dAp) return fail(h, B200SP_ERR_INVALID, "bad argument");
+  if (dtype != B200SP_R_32F && dtype != B200SP_R_64F) return fail(h, B200SP_ERR_INVALID, "unsupported dtype %d", dtype);
+  if (m == 0 || nnz == 0) return B200SP_OK;
+  DeviceGuard guard(h->device);
+  TRY(ensure(h, h->ws2, 256));
+  int *flag = (int *)h->ws2.ptr;
+  CUDA_TRY(h, cudaMemsetAsync(flag, 0, sizeof(int), h->stream));
+  const size_t vs = dtype == B200SP_R_32F ? 4 : 8;
+  const int cap = 16384;
+  const size_t smem = (size_t)cap * (vs + 4);
+  const int grid = std::max(1, std::min((int)m, NUM_SMS * 2));
+  if (dtype == B200SP_R_32F) {
+    TRY(set_smem(h, k_csr_sort_rows<float>, smem));
+    k_csr_sort_rows<float><<<grid, 256, smem, h->stream>>>((int)m, cap, dAp, dAj, (float *)dAx, flag);
+  } else {
+    TRY(set_smem(h, k_csr_sort_rows<double>, smem));
+    k_csr_sort_rows<double><<<grid, 256, smem, h->stream>>>((int)m, cap, dAp, dAj, (double *)dAx, flag);
+  }
+  TRY(check_launch(h, "k_csr_sort_rows"));
+  int too_long = 0;
+  CUDA_TRY(h, cudaMemcpyAsync(&too_long, flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+  if (too_long) return fail(h, B200SP_ERR_INVALID, "csr_sort_indices: an unsorted row has more than %d entries", cap);
+  return B200SP_OK;
+}
+
+// ================================================================= host-buffer one-shots ====
+
+namespace {
+
+int ensure_pinned(b200sp_context *h, int i, size_t bytes) {
+  if (bytes <= h->pinned_out_size[i]) return B200SP_OK;
+  if (h->pinned_out[i]) cudaFreeHost(h->pinned_out[i]);
+  h->pinned_out[i] = nullptr;
+  h->pinned_out_size[i] = 0;
+  const size_t want = std::max<size_t>(align_up(bytes, 4096), 4096);
+  if (cudaMallocHost(&h->pinned_out[i], want) != cudaSuccess) {
+    cudaGetLastError();
+    return fail(h, B200SP_ERR_ALLOC, "out of pinned host memory allocating %zu bytes", want);
+  }
+  h->pinned_out_size[i] = want;
+  return B200SP_OK;
+}
+
+int upload(b200sp_context *h, Buffer &b, const void *src, size_t bytes) {
+  TRY(ensure(h, b, std::max<size_t>(bytes, 16)));
+  if (bytes) CUDA_TRY(h, cudaMemcpyAsync(b.ptr, src, bytes, cudaMemcpyHostToDevice, h->stream));
+  return B200SP_OK;
+}
+
+}  // namespace
+
+extern "C" int b200sp_spgemm_host(b200sp_handle_t h, int dtype, int64_t m, int64_t k, int64_t n,
+                                  const int32_t *hAp, const int32_t *hAj, const void *hAx,
+                                  const int32_t *hBp, const int32_t *hBj, const void *hBx, int alg,
+                                  float chunk_fraction, const void *alpha, int32_t **hCp, int32_t **hCj,
+                                  void **hCx, int64_t *nnzC, int64_t *num_products) {
+  if (!h) return B200SP_ERR_INVALID;
+  if (!hAp || !hBp || !hCp || !hCj || !hCx || !nnzC || m < 0 || k < 0 || n < 0)
+    return fail(h, B200SP_ERR_INVALID, "bad argument");
+  if (dtype != B200SP_R_32F && dtype != B200SP_R_64F) return fail(h, B200SP_ERR_INVALID, "unsupported dtype %d", dtype);
+  const size_t vs = dtype == B200SP_R_32F ? 4 : 8;
+  const int64_t nnzA = hAp[m], nnzB = hBp[k];
+  if (nnzA < 0 || nnzB < 0 || (nnzA && (!hAj || !hAx)) || (nnzB && (!hBj || !hBx)))
+    return fail(h, B200SP_ERR_INVALID, "bad CSR arrays");
+  DeviceGuard guard(h->device);
+  const bool alias = (hAp == hBp && hAj == hBj && hAx == hBx && m == k);
+  TRY(upload(h, h->io[0], hAp, (size_t)(m + 1) * 4));
+  TRY(upload(h, h->io[1], hAj, (size_t)nnzA * 4));
+  TRY(upload(h, h->io[2], hAx, (size_t)nnzA * vs));
+  if (!alias) {
+    TRY(upload(h, h->io[3], hBp, (size_t)(k + 1) * 4));
+    TRY(upload(h, h->io[4], hBj, (size_t)nnzB * 4));
+    TRY(upload(h, h->io[5], hBx, (size_t)nnzB * vs));
+  }
+  const int bi = alias ? 0 : 3;
+  TRY(ensure(h, h->io[6], (size_t)(m + 1) * 4));
+  int64_t nc = 0;
+  TRY(b200sp_spgemm_symbolic(h, m, k, n, nnzA, nnzB, (const int *)h->io[0].ptr, (const int *)h->io[1].ptr,
+                             (const int *)h->io[bi].ptr, (const int *)h->io[bi + 1].ptr, alg, chunk_fraction,
+                             num_products, &nc, (int *)h->io[6].ptr));
+  TRY(ensure(h, h->io[7], std::max<size_t>((size_t)nc * 4, 16)));
+  TRY(ensure(h, h->io[8], std::max<size_t>((size_t)nc * vs, 16)));
+  TRY(b200sp_spgemm_numeric(h, dtype, alpha, h->io[2].ptr, h->io[bi + 2].ptr, (int *)h->io[7].ptr, h->io[8].ptr));
+  TRY(ensure_pinned(h, 0, (size_t)(m + 1) * 4));
+  TRY(ensure_pinned(h, 1, (size_t)nc * 4));
+  TRY(ensure_pinned(h, 2, (size_t)nc * vs));
+  CUDA_TRY(h, cudaMemcpyAsync(h->pinned_out[0], h->io[6].ptr, (size_t)(m + 1) * 4, cudaMemcpyDeviceToHost, h->stream));
+  if (nc) {
+    CUDA_TRY(h, cudaMemcpyAsync(h->pinned_out[1], h->io[7].ptr, (size_t)nc * 4, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(h->pinned_out[2], h->io[8].ptr, (size_t)nc * vs, cudaMemcpyDeviceToHost, h->stream));
+  }
+  CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+  *hCp = (int32_t *)h->pinned_out[0];
+  *hCj = (int32_t *)h->pinned_out[1];
+  *hCx = h->pinned_out[2];
+  *nnzC = nc;
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_spmv_host(b200sp_handle_t h, int dtype, int64_t m, int64_t n, int64_t nnz,
+                                const int32_t *hAp, const int32_t *hAj, const void *hAx, const void *hx,
+                                void *hy, const void *alpha, const void *beta) {
+  if (!h) return B200SP_ERR_INVALID;
+  if (!hAp || !hy || m < 0 || n < 0 || nnz < 0 || (nnz && (!hAj || !hAx || !hx))) return fail(h, B200SP_ERR_INVALID, "bad argument");
+  if (dtype != B200SP_R_32F && dtype != B200SP_R_64F) return fail(h, B200SP_ERR_INVALID, "unsupported dtype %d", dtype);
+  const size_t vs = dtype == B200SP_R_32F ? 4 : 8;
+  DeviceGuard guard(h->device);
+  TRY(upload(h, h->io[0], hAp, (size_t)(m + 1) * 4));
+  TRY(upload(h, h->io[1], hAj, (size_t)nnz * 4));
+  TRY(upload(h, h->io[2], hAx, (size_t)nnz * vs));
+  TRY(upload(h, h->io[3], hx, (size_t)n * vs));
+  const bool beta_zero = !beta || (dtype == B200SP_R_32F ? *(const float *)beta == 0.f : *(const double *)beta == 0.0);
+  if (beta_zero) TRY(ensure(h, h->io[4], std::max<size_t>((size_t)m * vs, 16)));
+  else TRY(upload(h, h->io[4], hy, (size_t)m * vs));
+  TRY(b200sp_spmv(h, dtype, m, n, nnz, (const int *)h->io[0].ptr, (const int *)h->io[1].ptr, h->io[2].ptr,
+                  h->io[3].ptr, h->io[4].ptr, alpha, beta));
+  if (m) CUDA_TRY(h, cudaMemcpyAsync(hy, h->io[4].ptr, (size_t)m * vs, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_free_host(void *ptr) {
+  free(ptr);
+  return B200SP_OK;
+}

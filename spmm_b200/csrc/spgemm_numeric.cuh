@@ -1,0 +1,321 @@
+// spgemm_numeric.cuh -- numeric Gustavson pass: C_i = sum_k a_ik * B_k with sorted columns.
+//
+// Takes the place of the value half of cusparseSpGEMM_compute and of cusparseSpGEMM_copy
+// (reference: cupy_cusparse/spgemm_from_txt_alg1.cu:177-188, cupyx/cusparse.py:2108-2137).
+//
+// Ordering contract (see common.cuh): every output entry is the sequential sum, in A-row
+// storage order, of separately rounded products.  That makes the values bit-identical to
+// scipy.sparse (the reference's CPU path) and run-to-run deterministic: no floating-point
+// atomics anywhere; parallelism comes from distinct columns only.
+#pragma once
+#include <limits.h>
+#include "common.cuh"
+
+namespace b200sp {
+
+template <typename T>
+__device__ __forceinline__ T scale_out(T alpha, T v) {
+  return alpha == T(1) ? v : mul_rn(alpha, v);
+}
+
+// In-place stable compaction of the valid (key != EMPTY) slots of a group's table to the
+// front; returns the number of valid entries.  Safe in place: the write position never
+// exceeds the read position and each G-slot chunk is read in full before it is written.
+template <int G, typename T>
+__device__ __forceinline__ int compact_table(int *keys, T *vals, int S) {
+  const int lane = lane_id();
+  const int sub = lane & (G - 1);
+  int n_valid = 0;
+  for (int c = 0; c < S; c += G) {
+    const int k = keys[c + sub];
+    const T v = vals[c + sub];
+    const bool valid = (k != EMPTY);
+    const unsigned bal = __ballot_sync(FULL, valid);
+    unsigned gb;
+    if (G == 32) gb = bal;
+    else gb = (bal >> (lane & ~(G - 1))) & ((1u << (G & 31)) - 1u);
+    const int pos = n_valid + __popc(gb & ((1u << sub) - 1u));
+    __syncwarp();
+    if (valid) {
+      keys[pos] = k;
+      vals[pos] = v;
+    }
+    n_valid += __popc(gb);
+    __syncwarp();
+  }
+  return n_valid;
+}
+
+// Bitonic sort of P = 2^x (key, val) pairs in shared memory by `nthr` threads (tid in
+// [0,nthr)); SYNC() is __syncwarp or __syncthreads.
+template <typename T, class SyncF>
+__device__ __forceinline__ void bitonic_sort(int *keys, T *vals, int P, int tid, int nthr,
+                                             SyncF &&sync) {
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = tid; t < (P >> 1); t += nthr) {
+        const int idx = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        const int ixj = idx | j;
+        const int ka = keys[idx], kb = keys[ixj];
+        const bool up = (idx & k) == 0;
+        if ((ka > kb) == up) {
+          keys[idx] = kb;
+          keys[ixj] = ka;
+          const T va = vals[idx];
+          vals[idx] = vals[ixj];
+          vals[ixj] = va;
+        }
+      }
+      sync();
+    }
+  }
+}
+
+// ---- group-of-G-lanes per row, hash accumulator of S slots per group ---------------------
+// G = 8,  S = 64   : rows of C with <= 32 entries (4 rows per warp), rank sort
+// G = 32, S = 256+ : rows of C with <= S/2 entries (warp per row), rank or bitonic sort
+template <int G, typename T>
+__global__ void __launch_bounds__(128)
+k_num_hash_group(const int *__restrict__ rows, int nrows, int S, const int *__restrict__ Ap,
+                 const int *__restrict__ Aj, const T *__restrict__ Ax,
+                 const int *__restrict__ Bp, const int *__restrict__ Bj,
+                 const T *__restrict__ Bx, const int *__restrict__ Cp, int *__restrict__ Cj,
+                 T *__restrict__ Cx, T alpha) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int groups_per_block = 128 / G;
+  const int g = threadIdx.x / G;
+  const int lane = lane_id();
+  const int sub = lane & (G - 1);
+  T *vals = reinterpret_cast<T *>(smem_raw) + g * S;
+  int *keys = reinterpret_cast<int *>(smem_raw + (size_t)groups_per_block * S * sizeof(T)) + g * S;
+  const unsigned mask = S - 1;
+  const int uid_base = (lane / G) * S;  // unique across the groups of this warp
+  const int ridx = blockIdx.x * groups_per_block + g;
+  const int row = ridx < nrows ? rows[ridx] : -1;
+  for (int s = sub; s < S; s += G) {
+    keys[s] = EMPTY;
+    vals[s] = T(0);
+  }
+  __syncwarp();
+  int a_begin = 0, a_end = 0;
+  if (row >= 0) {
+    a_begin = __ldg(Ap + row);
+    a_end = __ldg(Ap + row + 1);
+  }
+  stream_products<G>(a_begin, a_end, Aj, Bp, [&](bool act, int bidx, int aidx, bool mc) {
+    int slot = 0;
+    T v = T(0);
+    if (act) {
+      bool fresh;
+      slot = hash_insert(keys, mask, __ldg(Bj + bidx), fresh);
+      v = mul_rn(__ldg(Ax + aidx), __ldg(Bx + bidx));
+    }
+    __syncwarp();  // inserts of this step are visible before the accumulate
+    ordered_add(vals, slot, uid_base + slot, act, v, mc);
+  });
+  const int nnz = compact_table<G, T>(keys, vals, S);
+  if (row < 0) return;
+  const int out = __ldg(Cp + row);
+  if (G < 32 || nnz <= 64) {
+    // rank sort: position = number of smaller keys (keys are distinct)
+    for (int e = sub; e < nnz; e += G) {
+      const int k = keys[e];
+      int rank = 0;
+      for (int f = 0; f < nnz; ++f) rank += (keys[f] < k);
+      Cj[out + rank] = k;
+      Cx[out + rank] = scale_out(alpha, vals[e]);
+    }
+  } else {
+    const int P = next_pow2(nnz);
+    for (int s = nnz + lane; s < P; s += 32) keys[s] = INT_MAX;
+    __syncwarp();
+    bitonic_sort(keys, vals, P, lane, 32, [] { __syncwarp(); });
+    for (int e = lane; e < nnz; e += 32) {
+      Cj[out + e] = keys[e];
+      Cx[out + e] = scale_out(alpha, vals[e]);
+    }
+  }
+}
+
+// ---- CTA per row, hash accumulator of S slots in shared memory -----------------------------
+// Rows of C with up to 0.75 * S entries.  The A nonzeros are walked one at a time (k-step):
+// all threads stride the one B row, whose columns are distinct, so every accumulator is
+// touched by at most one thread per step and the barrier between steps fixes the order.
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_num_hash_cta(const int *__restrict__ rows, int nrows, int S, const int *__restrict__ Ap,
+               const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
+               const int *__restrict__ Bj, const T *__restrict__ Bx, const int *__restrict__ Cp,
+               int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int s_start[256];
+  __shared__ int s_len[256];
+  __shared__ int s_nnz;
+  T *vals = reinterpret_cast<T *>(smem_raw);
+  int *keys = reinterpret_cast<int *>(smem_raw + (size_t)S * sizeof(T));
+  const unsigned mask = S - 1;
+  const int tid = threadIdx.x;
+  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
+    const int row = rows[ridx];
+    for (int s = tid; s < S; s += 256) {
+      keys[s] = EMPTY;
+      vals[s] = T(0);
+    }
+    const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
+    __syncthreads();
+    for (int base = a_begin; base < a_end; base += 256) {
+      const int t = base + tid;
+      int st = 0, ln = 0;
+      if (t < a_end) {
+        const int kk = __ldg(Aj + t);
+        st = __ldg(Bp + kk);
+        ln = __ldg(Bp + kk + 1) - st;
+      }
+      s_start[tid] = st;
+      s_len[tid] = ln;
+      __syncthreads();
+      const int cnt = min(256, a_end - base);
+      for (int q = 0; q < cnt; ++q) {
+        const int ql = s_len[q];
+        if (ql == 0) continue;  // CTA-uniform
+        const int qs = s_start[q];
+        const T a = __ldg(Ax + base + q);
+        for (int u = tid; u < ql; u += 256) {
+          bool fresh;
+          const int slot = hash_insert(keys, mask, __ldg(Bj + qs + u), fresh);
+          vals[slot] = add_rn(vals[slot], mul_rn(a, __ldg(Bx + qs + u)));
+        }
+        __syncthreads();
+      }
+      __syncthreads();
+    }
+    // compact (warp 0, in place), then sort with the whole CTA
+    if (tid < 32) {
+      const int nn = compact_table<32, T>(keys, vals, S);
+      if (tid == 0) s_nnz = nn;
+    }
+    __syncthreads();
+    const int nnz = s_nnz;
+    const int P = next_pow2(nnz);
+    for (int s = nnz + tid; s < P; s += 256) keys[s] = INT_MAX;
+    __syncthreads();
+    bitonic_sort(keys, vals, P, tid, 256, [] { __syncthreads(); });
+    const int out = __ldg(Cp + row);
+    for (int e = tid; e < nnz; e += 256) {
+      Cj[out + e] = keys[e];
+      Cx[out + e] = scale_out(alpha, vals[e]);
+    }
+    __syncthreads();
+  }
+}
+
+// ---- CTA per row, bitmap + rank, everything in global memory (any n, any row size) ---------
+// Fallback for rows too large for a shared-memory table.  Per CTA workspace: nwords bitmap
+// words + nwords exclusive popcount prefixes.  The rank of column j among the set bits is its
+// position in the sorted output row, so values accumulate straight into C.data (no hash, no
+// sort), ordered by the same k-step barrier as above.  The bitmap is zero on entry to each row.
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_num_bitmap_global(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
+                    const int *__restrict__ Aj, const T *__restrict__ Ax,
+                    const int *__restrict__ Bp, const int *__restrict__ Bj,
+                    const T *__restrict__ Bx, const int *__restrict__ Cp, int *__restrict__ Cj,
+                    T *Cx, T alpha, unsigned *__restrict__ gws) {
+  __shared__ int s_start[256];
+  __shared__ int s_len[256];
+  __shared__ int s_scan[9];
+  const int nwords = (n + 31) >> 5;
+  unsigned *bm = gws + (size_t)blockIdx.x * 2 * nwords;
+  int *prefix = reinterpret_cast<int *>(bm + nwords);
+  const int tid = threadIdx.x, lane = lane_id(), w = tid >> 5;
+  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
+    const int row = rows[ridx];
+    const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
+    const int out = __ldg(Cp + row), nnz = __ldg(Cp + row + 1) - out;
+    // (1) structure: set bits, warps take whole B rows
+    for (int t = a_begin + w; t < a_end; t += 8) {
+      const int kk = __ldg(Aj + t);
+      const int be = __ldg(Bp + kk + 1);
+      for (int u = __ldg(Bp + kk) + lane; u < be; u += 32) {
+        const int j = __ldg(Bj + u);
+        atomicOr(&bm[j >> 5], 1u << (j & 31));
+      }
+    }
+    for (int e = tid; e < nnz; e += 256) Cx[out + e] = T(0);
+    __syncthreads();
+    // (2) exclusive prefix of the per-word popcounts (block scan with carry)
+    int carry = 0;
+    for (int s0 = 0; s0 < nwords; s0 += 256) {
+      const int s = s0 + tid;
+      const int c = s < nwords ? __popc(__ldcg(bm + s)) : 0;
+      int incl = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(FULL, incl, o);
+        if (lane >= o) incl += v;
+      }
+      if (lane == 31) s_scan[w] = incl;
+      __syncthreads();
+      if (tid == 0) {
+        int run = 0;
+        for (int q = 0; q < 8; ++q) {
+          const int x = s_scan[q];
+          s_scan[q] = run;
+          run += x;
+        }
+        s_scan[8] = run;
+      }
+      __syncthreads();
+      if (s < nwords) prefix[s] = carry + s_scan[w] + incl - c;
+      carry += s_scan[8];
+      __syncthreads();
+    }
+    // (3) ordered accumulation, one A nonzero per step
+    for (int base = a_begin; base < a_end; base += 256) {
+      const int t = base + tid;
+      int st = 0, ln = 0;
+      if (t < a_end) {
+        const int kk = __ldg(Aj + t);
+        st = __ldg(Bp + kk);
+        ln = __ldg(Bp + kk + 1) - st;
+      }
+      s_start[tid] = st;
+      s_len[tid] = ln;
+      __syncthreads();
+      const int cnt = min(256, a_end - base);
+      for (int q = 0; q < cnt; ++q) {
+        const int ql = s_len[q];
+        if (ql == 0) continue;
+        const int qs = s_start[q];
+        const T a = __ldg(Ax + base + q);
+        for (int u = tid; u < ql; u += 256) {
+          const int j = __ldg(Bj + qs + u);
+          const unsigned bits = __ldcg(bm + (j >> 5));
+          const int r = __ldcg(prefix + (j >> 5)) + __popc(bits & ((1u << (j & 31)) - 1u));
+          T *dst = Cx + out + r;
+          __stcg(dst, add_rn(__ldcg(dst), mul_rn(a, __ldg(Bx + qs + u))));
+        }
+        __syncthreads();
+      }
+      __syncthreads();
+    }
+    // (4) emit sorted columns, scale, and clear the bitmap for the next row
+    for (int s = tid; s < nwords; s += 256) {
+      unsigned bits = __ldcg(bm + s);
+      if (bits) {
+        int p = out + __ldcg(prefix + s);
+        bm[s] = 0u;
+        while (bits) {
+          const int b = __ffs(bits) - 1;
+          bits &= bits - 1;
+          Cj[p++] = (s << 5) + b;
+        }
+      }
+    }
+    if (alpha != T(1))
+      for (int e = tid; e < nnz; e += 256) Cx[out + e] = mul_rn(alpha, __ldcg(Cx + out + e));
+    __syncthreads();
+  }
+}
+
+}  // namespace b200sp

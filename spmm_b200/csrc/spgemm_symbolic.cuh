@@ -1,0 +1,132 @@
+// spgemm_symbolic.cuh -- exact nnz(C_i) per row (symbolic pass 2).
+//
+// Takes the place of the structure half of cusparseSpGEMM_compute
+// (reference: cupy_cusparse/spgemm_from_txt_alg1.cu:177-181).  No value is touched here, so
+// insertion order is free and all kernels use the whole group/CTA in parallel.
+// The count of row r is written to Cp[r]; the scan turns the counts into C.indptr.
+#pragma once
+#include "common.cuh"
+
+namespace b200sp {
+
+// ---- group-of-G-lanes per row, hash set of S slots per group in shared memory ------------
+// G = 8,  S = 64   : rows with <= 32 candidate columns  (4 rows per warp)
+// G = 32, S = 256+ : rows with <= S/2 candidate columns (warp per row)
+template <int G>
+__global__ void __launch_bounds__(128)
+k_sym_hash_group(const int *__restrict__ rows, int nrows, int S, const int *__restrict__ Ap,
+                 const int *__restrict__ Aj, const int *__restrict__ Bp,
+                 const int *__restrict__ Bj, int *__restrict__ Cp) {
+  extern __shared__ int smem_i[];
+  const int groups_per_block = 128 / G;
+  const int g = threadIdx.x / G;
+  const int sub = threadIdx.x & (G - 1);
+  int *keys = smem_i + g * S;
+  const unsigned mask = S - 1;
+  const int ridx = blockIdx.x * groups_per_block + g;
+  const int row = ridx < nrows ? rows[ridx] : -1;
+  for (int s = sub; s < S; s += G) keys[s] = EMPTY;
+  __syncwarp();
+  int a_begin = 0, a_end = 0;
+  if (row >= 0) {
+    a_begin = __ldg(Ap + row);
+    a_end = __ldg(Ap + row + 1);
+  }
+  int cnt = 0;
+  stream_products<G>(a_begin, a_end, Aj, Bp, [&](bool act, int bidx, int, bool) {
+    if (act) {
+      bool fresh;
+      hash_insert(keys, mask, __ldg(Bj + bidx), fresh);
+      cnt += fresh;
+    }
+  });
+  cnt = group_sum<G>(cnt);
+  if (row >= 0 && sub == 0) Cp[row] = cnt;
+}
+
+// ---- CTA per row, hash set of S slots in shared memory ------------------------------------
+// Each warp takes whole rows of B (A nonzero q = warp, warp + W, ...) and strides them.
+__global__ void __launch_bounds__(256)
+k_sym_hash_cta(const int *__restrict__ rows, int nrows, int S, const int *__restrict__ Ap,
+               const int *__restrict__ Aj, const int *__restrict__ Bp,
+               const int *__restrict__ Bj, int *__restrict__ Cp) {
+  extern __shared__ int smem_i[];
+  __shared__ int s_cnt;
+  int *keys = smem_i;
+  const unsigned mask = S - 1;
+  const int lane = lane_id(), w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
+    const int row = rows[ridx];
+    for (int s = threadIdx.x; s < S; s += blockDim.x) keys[s] = EMPTY;
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    const int a_end = __ldg(Ap + row + 1);
+    int cnt = 0;
+    for (int t = __ldg(Ap + row) + w; t < a_end; t += nw) {
+      const int kk = __ldg(Aj + t);
+      const int be = __ldg(Bp + kk + 1);
+      for (int u = __ldg(Bp + kk) + lane; u < be; u += 32) {
+        bool fresh;
+        hash_insert(keys, mask, __ldg(Bj + u), fresh);
+        cnt += fresh;
+      }
+    }
+    cnt = warp_sum(cnt);
+    if (lane == 0 && cnt) atomicAdd(&s_cnt, cnt);
+    __syncthreads();
+    if (threadIdx.x == 0) Cp[row] = s_cnt;
+    __syncthreads();
+  }
+}
+
+// ---- CTA per row, bitmap over the n columns -----------------------------------------------
+// SMEM = true : bitmap in dynamic shared memory (n/8 bytes; n <= ~1.7 M columns)
+// SMEM = false: bitmap in the CTA's slice of the global workspace (any n); persistent grid.
+// The bitmap is zero on entry to every row: the count sweep clears what it counts.
+template <bool SMEM>
+__global__ void __launch_bounds__(256)
+k_sym_bitmap_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
+                 const int *__restrict__ Aj, const int *__restrict__ Bp,
+                 const int *__restrict__ Bj, int *__restrict__ Cp, unsigned *__restrict__ gws) {
+  extern __shared__ int smem_i[];
+  __shared__ int s_cnt;
+  const int nwords = (n + 31) >> 5;
+  unsigned *bm = SMEM ? reinterpret_cast<unsigned *>(smem_i) : gws + (size_t)blockIdx.x * nwords;
+  const int lane = lane_id(), w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (SMEM) {
+    for (int s = threadIdx.x; s < nwords; s += blockDim.x) bm[s] = 0u;
+  }  // the global workspace is zeroed by the host before launch
+  if (threadIdx.x == 0) s_cnt = 0;
+  __syncthreads();
+  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
+    const int row = rows[ridx];
+    const int a_end = __ldg(Ap + row + 1);
+    for (int t = __ldg(Ap + row) + w; t < a_end; t += nw) {
+      const int kk = __ldg(Aj + t);
+      const int be = __ldg(Bp + kk + 1);
+      for (int u = __ldg(Bp + kk) + lane; u < be; u += 32) {
+        const int j = __ldg(Bj + u);
+        atomicOr(&bm[j >> 5], 1u << (j & 31));
+      }
+    }
+    __syncthreads();
+    int cnt = 0;
+    for (int s = threadIdx.x; s < nwords; s += blockDim.x) {
+      const unsigned bits = SMEM ? bm[s] : __ldcg(bm + s);
+      if (bits) {
+        cnt += __popc(bits);
+        bm[s] = 0u;
+      }
+    }
+    cnt = warp_sum(cnt);
+    if (lane == 0 && cnt) atomicAdd(&s_cnt, cnt);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      Cp[row] = s_cnt;
+      s_cnt = 0;
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace b200sp
