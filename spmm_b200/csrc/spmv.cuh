@@ -122,6 +122,7 @@ k_spmv_stream(int m, int nnz, const int *__restrict__ Ap, const int *__restrict_
   if (r_hi - r_lo + 1 >= 64) {  // many short rows: one thread per row
     for (int r = r_lo + tid; r <= r_hi; r += SPMV_THREADS) {
       const int b = max(__ldg(Ap + r), t0), e = min(__ldg(Ap + r + 1), t1);
+      if (e <= b) continue;  // empty row: k_spmv_empty_rows owns it
       T sum = T(0);
       for (int q = b; q < e; ++q) sum += s_prod[q - t0];
       spmv_emit(r, sum, r_lo, r_hi, first_cont, last_open, y, alpha, beta, carry_val, tail_val);
@@ -130,6 +131,7 @@ k_spmv_stream(int m, int nnz, const int *__restrict__ Ap, const int *__restrict_
     const int lane = tid & 31, w = tid >> 5;
     for (int r = r_lo + w; r <= r_hi; r += SPMV_THREADS / 32) {
       const int b = max(__ldg(Ap + r), t0), e = min(__ldg(Ap + r + 1), t1);
+      if (e <= b) continue;  // empty row (warp-uniform)
       T sum = T(0);
       for (int q = b + lane; q < e; q += 32) sum += s_prod[q - t0];
 #pragma unroll
