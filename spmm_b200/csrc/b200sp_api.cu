@@ -29,6 +29,7 @@ namespace {
 
 constexpr size_t SMEM_MAX = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100
 constexpr size_t SMEM_BITMAP_MAX = 200 * 1024;  // budget for an n-bit bitmap in shared memory
+constexpr size_t SMEM_DENSE_MAX = 208 * 1024;   // budget for an n-column dense accumulator
 
 struct Buffer {  // grow-only device buffer
   void *ptr = nullptr;
@@ -36,7 +37,7 @@ struct Buffer {  // grow-only device buffer
 };
 
 enum SymKind { SYM_GROUP8, SYM_WARP, SYM_CTA_HASH, SYM_CTA_BITMAP };
-enum NumKind { NUM_GROUP8, NUM_WARP, NUM_CTA_HASH, NUM_GLOBAL };
+enum NumKind { NUM_GROUP8, NUM_WARP, NUM_CTA_HASH, NUM_GLOBAL, NUM_DENSE };
 
 struct BinPlan {
   int kind;
@@ -328,6 +329,13 @@ void plan_bins(Plan &p) {
   p.num_bins[3] = {NUM_CTA_HASH, 8192};
   p.num_bins[4] = {NUM_CTA_HASH, 16384};
   p.num_bins[5] = {NUM_GLOBAL, 0};
+  if ((size_t)p.n * 4 <= SMEM_DENSE_MAX) {
+    // few columns: rows above 512 entries use the dense shared-memory accumulator (no sort)
+    const int dl[4] = {32, 128, 512, INT_MAX};
+    p.num_limits.nbins = 4;
+    for (int b = 0; b < 4; ++b) p.num_limits.limit[b] = dl[b];
+    p.num_bins[3] = {NUM_DENSE, 0};
+  }
 }
 
 int persistent_grid(int nrows, size_t smem_bytes) {
@@ -400,6 +408,16 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       k_num_hash_cta<T><<<persistent_grid(cnt, smem + 2304), 256, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
       return check_launch(h, "k_num_hash_cta");
     }
+    case NUM_DENSE:
+      if ((size_t)p.n * sizeof(T) <= SMEM_DENSE_MAX) {
+        const size_t smem = (size_t)p.n * sizeof(T);
+        const double avgB = p.k ? (double)p.nnzB / (double)p.k : 0.0;
+        const int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
+        TRY(set_smem(h, k_num_dense_cta<T>, smem));
+        k_num_dense_cta<T><<<persistent_grid(cnt, smem + 2304), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+        return check_launch(h, "k_num_dense_cta");
+      }
+      // fp64 with n between the fp32 and fp64 budgets: fall through to the global kernel
     case NUM_GLOBAL: {
       const size_t bytes = (size_t)((p.n + 31) / 32) * 8;  // bitmap + prefix
       int grid = std::max(1, std::min(cnt, 2 * NUM_SMS / p.num_chunks));

@@ -318,4 +318,121 @@ k_num_bitmap_global(const int *__restrict__ rows, int nrows, int n, const int *_
   }
 }
 
+// ---- CTA per row, dense accumulator over the n columns in shared memory ---------------------
+// For matrices whose column count fits shared memory (n * sizeof(T) <= ~200 KB) and rows of C
+// with more than a few hundred entries: slot = column, so there is no hashing, no probing and
+// no sort - the output sweep walks the columns in order.  "Untouched" is a reserved NaN bit
+// pattern that arithmetic cannot produce (the hardware returns the canonical NaN for invalid
+// operations and NaN operands), so explicit zeros from cancellation stay stored and no flag
+// array or atomic is needed.  The A nonzeros are applied one B row at a time with a barrier
+// in between (columns inside a B row are distinct); loads of R consecutive B rows are issued
+// together so the barrier chain never waits on L2.
+template <typename T> struct Untouched;
+template <> struct Untouched<float> {
+  static __device__ __forceinline__ float value() { return __int_as_float(0xFFC0DEAD); }
+  static __device__ __forceinline__ bool is(float v) { return __float_as_int(v) == (int)0xFFC0DEAD; }
+};
+template <> struct Untouched<double> {
+  static __device__ __forceinline__ double value() { return __longlong_as_double(0xFFF8DEADBEEF0001LL); }
+  static __device__ __forceinline__ bool is(double v) { return __double_as_longlong(v) == (long long)0xFFF8DEADBEEF0001LL; }
+};
+
+constexpr int DENSE_R = 4;       // B rows whose loads are in flight together
+constexpr int DENSE_MAX_NT = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(DENSE_MAX_NT, 1)
+k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
+                const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
+                const int *__restrict__ Bj, const T *__restrict__ Bx, const int *__restrict__ Cp,
+                int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int s_start[DENSE_MAX_NT];
+  __shared__ int s_len[DENSE_MAX_NT];
+  __shared__ int s_wcnt[DENSE_MAX_NT / 32];
+  T *acc = reinterpret_cast<T *>(smem_raw);
+  const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
+  const T UNT = Untouched<T>::value();
+  for (int c = tid; c < n; c += NT) acc[c] = UNT;
+  // columns per warp for the output sweep, a multiple of 32
+  const int cpw = ((n + nw - 1) / nw + 31) & ~31;
+  __syncthreads();
+  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
+    const int row = rows[ridx];
+    const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
+    for (int base = a_begin; base < a_end; base += NT) {
+      const int t = base + tid;
+      int st = 0, ln = 0;
+      if (t < a_end) {
+        const int kk = __ldg(Aj + t);
+        st = __ldg(Bp + kk);
+        ln = __ldg(Bp + kk + 1) - st;
+      }
+      s_start[tid] = st;
+      s_len[tid] = ln;
+      __syncthreads();
+      const int cnt = min(NT, a_end - base);
+      for (int q0 = 0; q0 < cnt; q0 += DENSE_R) {
+        int jr[DENSE_R];
+        T br[DENSE_R], ar[DENSE_R];
+#pragma unroll
+        for (int r = 0; r < DENSE_R; ++r) {  // issue the loads of R rows of B together
+          jr[r] = -1;
+          if (q0 + r < cnt && tid < s_len[q0 + r]) {
+            const int idx = s_start[q0 + r] + tid;
+            jr[r] = __ldg(Bj + idx);
+            br[r] = __ldg(Bx + idx);
+            ar[r] = __ldg(Ax + base + q0 + r);
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < DENSE_R; ++r) {
+          const int ql = (q0 + r < cnt) ? s_len[q0 + r] : 0;
+          if (ql == 0) continue;           // CTA-uniform
+          if (jr[r] >= 0) {
+            const T cur = acc[jr[r]];
+            acc[jr[r]] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, mul_rn(ar[r], br[r]));
+          }
+          if (ql > NT) {                   // long B row: the remaining strides, loaded in line
+            const int qs = s_start[q0 + r];
+            const T a = __ldg(Ax + base + q0 + r);
+            for (int u = tid + NT; u < ql; u += NT) {
+              const int j = __ldg(Bj + qs + u);
+              const T cur = acc[j];
+              acc[j] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, mul_rn(a, __ldg(Bx + qs + u)));
+            }
+          }
+          __syncthreads();
+        }
+      }
+      __syncthreads();
+    }
+    // ---- output: warp w owns columns [w*cpw, (w+1)*cpw); count, prefix, then ordered emit ----
+    const int c_lo = min(w * cpw, n), c_hi = min(c_lo + cpw, n);
+    int mine = 0;
+    for (int c = c_lo; c < c_hi; c += 32) {
+      const bool touched = (c + lane < c_hi) && !Untouched<T>::is(acc[c + lane]);
+      mine += __popc(__ballot_sync(FULL, touched));
+    }
+    if (lane == 0) s_wcnt[w] = mine;
+    __syncthreads();
+    int pos = __ldg(Cp + row);
+    for (int q = 0; q < w; ++q) pos += s_wcnt[q];
+    for (int c = c_lo; c < c_hi; c += 32) {
+      T v = UNT;
+      if (c + lane < c_hi) v = acc[c + lane];
+      const bool touched = !Untouched<T>::is(v);
+      const unsigned bal = __ballot_sync(FULL, touched);
+      if (touched) {
+        const int o = pos + __popc(bal & ((1u << lane) - 1u));
+        Cj[o] = c + lane;
+        Cx[o] = scale_out(alpha, v);
+        acc[c + lane] = UNT;
+      }
+      pos += __popc(bal);
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace b200sp
