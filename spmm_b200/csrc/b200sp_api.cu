@@ -367,6 +367,12 @@ int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
     }
     case SYM_CTA_BITMAP: {
       const size_t bytes = (size_t)((p.n + 31) / 32) * 4;
+      const size_t fbytes = (size_t)((p.n + 3) / 4) * 4;  // one byte flag per column
+      if (fbytes <= SMEM_BITMAP_MAX) {
+        TRY(set_smem(h, k_sym_flags_cta, fbytes));
+        k_sym_flags_cta<<<persistent_grid(cnt, fbytes + 64), 256, fbytes, st>>>(rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp);
+        return check_launch(h, "k_sym_flags_cta");
+      }
       if (bytes <= SMEM_BITMAP_MAX) {
         TRY(set_smem(h, k_sym_bitmap_cta<true>, bytes));
         k_sym_bitmap_cta<true><<<persistent_grid(cnt, bytes + 64), 256, bytes, st>>>(
@@ -414,7 +420,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         const double avgB = p.k ? (double)p.nnzB / (double)p.k : 0.0;
         const int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
         TRY(set_smem(h, k_num_dense_cta<T>, smem));
-        k_num_dense_cta<T><<<persistent_grid(cnt, smem + 2304), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+        k_num_dense_cta<T><<<persistent_grid(cnt, smem + 4352), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
         return check_launch(h, "k_num_dense_cta");
       }
       // fp64 with n between the fp32 and fp64 budgets: fall through to the global kernel
@@ -533,8 +539,9 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
     off += cnt;
   }
   // counts -> indptr
-  if (ntiles <= 16) {
-    k_scan_single<<<1, SCAN_THREADS, 0, st>>>(dCp, p.m, ctr);
+  const bool small_scan = p.m <= SCAN1_THREADS * SCAN1_MAX_ITEMS;
+  if (small_scan) {  // also fills the numeric-bin histogram
+    k_scan_single<<<1, SCAN1_THREADS, 0, st>>>(dCp, p.m, p.num_limits, ctr);
     TRY(check_launch(h, "k_scan_single"));
   } else {
     k_scan_tile_sums<<<ntiles, SCAN_THREADS, 0, st>>>(dCp, p.m, tile_sums);
@@ -544,8 +551,10 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
     k_scan_apply<<<ntiles, SCAN_THREADS, 0, st>>>(dCp, p.m, tile_sums);
     TRY(check_launch(h, "k_scan_apply"));
   }
-  k_hist_numeric<<<sgrid, 256, 0, st>>>(p.m, dCp, p.num_limits, ctr);
-  TRY(check_launch(h, "k_hist_numeric"));
+  if (!small_scan) {
+    k_hist_numeric<<<sgrid, 256, 0, st>>>(p.m, dCp, p.num_limits, ctr);
+    TRY(check_launch(h, "k_hist_numeric"));
+  }
   k_scatter_rows<true><<<sgrid, 256, 0, st>>>(p.m, dCp, p.num_limits, ctr, p.rows_num);
   TRY(check_launch(h, "k_scatter_rows<num>"));
   cudaEventRecord(h->ev[1], st);

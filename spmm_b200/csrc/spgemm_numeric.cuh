@@ -337,8 +337,8 @@ template <> struct Untouched<double> {
   static __device__ __forceinline__ bool is(double v) { return __double_as_longlong(v) == (long long)0xFFF8DEADBEEF0001LL; }
 };
 
-constexpr int DENSE_R = 4;       // B rows whose loads are in flight together
 constexpr int DENSE_MAX_NT = 256;
+constexpr int DENSE_PAD = 8;  // zero-length staging entries after the chunk (prefetch runs ahead)
 
 template <typename T>
 __global__ void __launch_bounds__(DENSE_MAX_NT, 1)
@@ -347,8 +347,8 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
                 const int *__restrict__ Bj, const T *__restrict__ Bx, const int *__restrict__ Cp,
                 int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ int s_start[DENSE_MAX_NT];
-  __shared__ int s_len[DENSE_MAX_NT];
+  __shared__ int2 s_seg[DENSE_MAX_NT + DENSE_PAD];  // {start, len} of the staged B rows
+  __shared__ T s_a[DENSE_MAX_NT + DENSE_PAD];       // their A values
   __shared__ int s_wcnt[DENSE_MAX_NT / 32];
   T *acc = reinterpret_cast<T *>(smem_raw);
   const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
@@ -357,56 +357,75 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
   // columns per warp for the output sweep, a multiple of 32
   const int cpw = ((n + nw - 1) / nw + 31) & ~31;
   __syncthreads();
+
+// One B row: this thread's entry (index clamped, so the loads need no branch) ...
+#define DENSE_FETCH(J, B, SG, Q)                                  \
+  {                                                               \
+    SG = s_seg[Q];                                                \
+    const int idx_ = SG.x + min(tid, max(SG.y - 1, 0));           \
+    J = __ldg(Bj + idx_);                                         \
+    B = __ldg(Bx + idx_);                                         \
+  }
+// ... applied in A-row order, one barrier per non-empty B row.
+#define DENSE_APPLY(J, B, SG, Q)                                                         \
+  if (SG.y) { /* CTA-uniform */                                                          \
+    const T a_ = s_a[Q];                                                                 \
+    if (tid < SG.y) {                                                                    \
+      const T cur_ = acc[J];                                                             \
+      acc[J] = add_rn(Untouched<T>::is(cur_) ? T(0) : cur_, mul_rn(a_, B));              \
+    }                                                                                    \
+    if (SG.y > NT) { /* long B row: remaining strides, loaded in line */                 \
+      for (int u_ = tid + NT; u_ < SG.y; u_ += NT) {                                     \
+        const int j_ = __ldg(Bj + SG.x + u_);                                            \
+        const T cur_ = acc[j_];                                                          \
+        acc[j_] = add_rn(Untouched<T>::is(cur_) ? T(0) : cur_, mul_rn(a_, __ldg(Bx + SG.x + u_))); \
+      }                                                                                  \
+    }                                                                                    \
+    __syncthreads();                                                                     \
+  }
+
   for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
     const int row = rows[ridx];
     const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
     for (int base = a_begin; base < a_end; base += NT) {
       const int t = base + tid;
-      int st = 0, ln = 0;
+      int2 sg = make_int2(0, 0);
+      T av = T(0);
       if (t < a_end) {
         const int kk = __ldg(Aj + t);
-        st = __ldg(Bp + kk);
-        ln = __ldg(Bp + kk + 1) - st;
+        const int st = __ldg(Bp + kk);
+        sg.y = __ldg(Bp + kk + 1) - st;
+        sg.x = sg.y ? st : 0;  // empty rows of B point at a safe address
+        av = __ldg(Ax + t);
       }
-      s_start[tid] = st;
-      s_len[tid] = ln;
+      s_seg[tid] = sg;
+      s_a[tid] = av;
+      if (tid < DENSE_PAD) s_seg[NT + tid] = make_int2(0, 0);
       __syncthreads();
-      const int cnt = min(NT, a_end - base);
-      for (int q0 = 0; q0 < cnt; q0 += DENSE_R) {
-        int jr[DENSE_R];
-        T br[DENSE_R], ar[DENSE_R];
-#pragma unroll
-        for (int r = 0; r < DENSE_R; ++r) {  // issue the loads of R rows of B together
-          jr[r] = -1;
-          if (q0 + r < cnt && tid < s_len[q0 + r]) {
-            const int idx = s_start[q0 + r] + tid;
-            jr[r] = __ldg(Bj + idx);
-            br[r] = __ldg(Bx + idx);
-            ar[r] = __ldg(Ax + base + q0 + r);
-          }
-        }
-#pragma unroll
-        for (int r = 0; r < DENSE_R; ++r) {
-          const int ql = (q0 + r < cnt) ? s_len[q0 + r] : 0;
-          if (ql == 0) continue;           // CTA-uniform
-          if (jr[r] >= 0) {
-            const T cur = acc[jr[r]];
-            acc[jr[r]] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, mul_rn(ar[r], br[r]));
-          }
-          if (ql > NT) {                   // long B row: the remaining strides, loaded in line
-            const int qs = s_start[q0 + r];
-            const T a = __ldg(Ax + base + q0 + r);
-            for (int u = tid + NT; u < ql; u += NT) {
-              const int j = __ldg(Bj + qs + u);
-              const T cur = acc[j];
-              acc[j] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, mul_rn(a, __ldg(Bx + qs + u)));
-            }
-          }
-          __syncthreads();
-        }
+      const int cnt = min(NT, a_end - base);  // entries [cnt, NT + PAD) have length 0
+      // rolling 4-deep register prefetch: the loads of B rows q+4.. are in flight while row q
+      // is applied, so the barrier chain does not wait on L2
+      int2 g0, g1, g2, g3;
+      int j0, j1, j2, j3;
+      T b0, b1, b2, b3;
+      DENSE_FETCH(j0, b0, g0, 0)
+      DENSE_FETCH(j1, b1, g1, 1)
+      DENSE_FETCH(j2, b2, g2, 2)
+      DENSE_FETCH(j3, b3, g3, 3)
+      for (int q = 0; q < cnt; q += 4) {
+        DENSE_APPLY(j0, b0, g0, q)
+        DENSE_FETCH(j0, b0, g0, q + 4)
+        DENSE_APPLY(j1, b1, g1, q + 1)
+        DENSE_FETCH(j1, b1, g1, q + 5)
+        DENSE_APPLY(j2, b2, g2, q + 2)
+        DENSE_FETCH(j2, b2, g2, q + 6)
+        DENSE_APPLY(j3, b3, g3, q + 3)
+        DENSE_FETCH(j3, b3, g3, q + 7)
       }
       __syncthreads();
     }
+#undef DENSE_FETCH
+#undef DENSE_APPLY
     // ---- output: warp w owns columns [w*cpw, (w+1)*cpw); count, prefix, then ordered emit ----
     const int c_lo = min(w * cpw, n), c_hi = min(c_lo + cpw, n);
     int mine = 0;

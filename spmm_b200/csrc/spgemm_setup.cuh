@@ -207,15 +207,36 @@ __device__ __forceinline__ long long scan_tile(int *Cp, int m, int tile_base, lo
   return carry + tile_total;
 }
 
-// Small m: one block walks the tiles with a carry.
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_single(int *Cp, int m, Counters *ctr) {
+// Small m (<= 64 K rows): one 1024-thread block, each thread owns a contiguous run of rows, one
+// block-wide scan.  Also builds the numeric-bin histogram of the row sizes (saves a launch).
+constexpr int SCAN1_THREADS = 1024;
+constexpr int SCAN1_MAX_ITEMS = 64;
+__global__ void __launch_bounds__(SCAN1_THREADS, 1)
+k_scan_single(int *Cp, int m, BinLimits bl, Counters *ctr) {
   __shared__ long long s_warp[33];
-  long long carry = 0;
-  for (int tb = 0; tb < m; tb += SCAN_TILE) carry = scan_tile(Cp, m, tb, carry, s_warp);
-  if (threadIdx.x == 0) {
-    Cp[m] = (int)carry;
-    ctr->nnz_c = (unsigned long long)carry;
+  __shared__ int s_hist[MAX_BINS];
+  if (threadIdx.x < MAX_BINS) s_hist[threadIdx.x] = 0;
+  __syncthreads();
+  const int per = (m + SCAN1_THREADS - 1) / SCAN1_THREADS;
+  const int b = threadIdx.x * per, e = min(b + per, m);
+  long long sum = 0;
+  for (int i = b; i < e; ++i) {
+    const int c = Cp[i];
+    sum += c;
+    if (c > 0) atomicAdd(&s_hist[classify(bl, c)], 1);
   }
+  long long total;
+  long long ex = block_exscan(sum, s_warp, &total);
+  for (int i = b; i < e; ++i) {
+    const int c = Cp[i];
+    Cp[i] = (int)ex;
+    ex += c;
+  }
+  if (threadIdx.x == 0) {
+    Cp[m] = (int)total;
+    ctr->nnz_c = (unsigned long long)total;
+  }
+  if (threadIdx.x < bl.nbins && s_hist[threadIdx.x]) ctr->num_count[threadIdx.x] = s_hist[threadIdx.x];
 }
 
 // Large m: (1) per-tile sums, (2) one block scans the tile sums, (3) per-tile scan + offset.

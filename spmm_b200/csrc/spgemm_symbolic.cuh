@@ -129,4 +129,49 @@ k_sym_bitmap_cta(const int *__restrict__ rows, int nrows, int n, const int *__re
   }
 }
 
+// ---- CTA per row, one byte flag per column in shared memory --------------------------------
+// For n <= ~200 K columns.  Marking a column is a plain byte store (idempotent, so no atomic
+// and no ordering between warps); the count is a popcount sweep over the flag words, which
+// also clears them for the next row.
+__global__ void __launch_bounds__(256, 2)
+k_sym_flags_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
+                const int *__restrict__ Aj, const int *__restrict__ Bp,
+                const int *__restrict__ Bj, int *__restrict__ Cp) {
+  extern __shared__ int smem_i[];
+  __shared__ int s_cnt;
+  unsigned char *flags = reinterpret_cast<unsigned char *>(smem_i);
+  unsigned *fw = reinterpret_cast<unsigned *>(smem_i);
+  const int nwords = (n + 3) >> 2;
+  const int lane = lane_id(), w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int s = threadIdx.x; s < nwords; s += blockDim.x) fw[s] = 0u;
+  if (threadIdx.x == 0) s_cnt = 0;
+  __syncthreads();
+  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
+    const int row = rows[ridx];
+    const int a_end = __ldg(Ap + row + 1);
+    for (int t = __ldg(Ap + row) + w; t < a_end; t += nw) {
+      const int kk = __ldg(Aj + t);
+      const int be = __ldg(Bp + kk + 1);
+      for (int u = __ldg(Bp + kk) + lane; u < be; u += 32) flags[__ldg(Bj + u)] = 1;
+    }
+    __syncthreads();
+    int cnt = 0;
+    for (int s = threadIdx.x; s < nwords; s += blockDim.x) {
+      const unsigned f = fw[s];
+      if (f) {
+        cnt += __popc(f);
+        fw[s] = 0u;
+      }
+    }
+    cnt = warp_sum(cnt);
+    if (lane == 0 && cnt) atomicAdd(&s_cnt, cnt);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      Cp[row] = s_cnt;
+      s_cnt = 0;
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace b200sp

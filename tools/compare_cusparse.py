@@ -1,0 +1,98 @@
+#!/usr/bin/env python3
+"""Side-by-side: libb200sp vs cuSPARSE ALG1/ALG2/ALG3 on the same device-resident inputs:
+time per SpGEMM and peak device memory beyond the inputs (workspace + output), the two axes of
+the reference's SpGEMM_alg_comparison (profiler.py:210-230).  Needs a GPU.
+
+  python tools/compare_cusparse.py [--cases c3_1e-4 c3_1e-3 c3_1e-2 c1 c4_1e-2 ...] [--out file.json]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+import spmm_b200  # noqa: E402
+from spmm_b200 import _lib  # noqa: E402
+
+EXE = os.path.join(ROOT, "tools", "_build", "cusparse_bench")
+
+
+def make(case):
+    if case == "c1":
+        return bench.profiler_matrix(4096, 4096, 1e-3)
+    if case.startswith("rmat"):
+        return bench.rmat_matrix(int(case[4:]))
+    kind, d = case.split("_")
+    n = {"c3": 16384, "c4": 8192}[kind]
+    return bench.profiler_matrix(n, n, float(d))
+
+
+def ours(A, alg, reps=7):
+    a = spmm_b200.csr_matrix(A)
+    a._canonical = True
+    ts = []
+    _lib.load().b200sp_reset_stats(_lib.handle(0))
+    for i in range(reps + 2):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        c = spmm_b200.cusparse.spgemm(a, a, alg=alg)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 2:
+            ts.append(e0.elapsed_time(e1))
+    s = _lib.stats(0)
+    out_bytes = 4 * (A.shape[0] + 1) + c.nnz * 8
+    return {"impl": "b200sp", "alg": alg, "ms_median": float(np.median(ts)), "ms_min": float(min(ts)), "nnzC": c.nnz,
+            "peak_bytes_excl_inputs": int(s.peak_workspace_bytes + out_bytes), "workspace_bytes": int(s.peak_workspace_bytes),
+            "products": int(s.num_products), "ms_symbolic": s.ms_symbolic, "ms_numeric": s.ms_numeric}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cases", nargs="+", default=["c3_1e-4", "c3_1e-3", "c3_1e-2"])
+    ap.add_argument("--out", default=None)
+    ap.add_argument("--reps", type=int, default=5)
+    args = ap.parse_args()
+    results = {}
+    for case in args.cases:
+        A = make(case)
+        rows = []
+        with tempfile.NamedTemporaryFile(suffix=".bin", delete=False) as f:
+            np.array([A.shape[0], A.shape[1], A.nnz], dtype=np.int64).tofile(f)
+            A.indptr.astype(np.int32).tofile(f)
+            A.indices.astype(np.int32).tofile(f)
+            A.data.astype(np.float32).tofile(f)
+            path = f.name
+        for alg in (1, 2, 3):
+            try:
+                out = subprocess.run([EXE, path, str(alg), "0.2", str(args.reps)], capture_output=True, text=True, timeout=600)
+                rows.append(json.loads(out.stdout.strip().splitlines()[-1]))
+            except Exception as e:
+                rows.append({"impl": "cusparse", "alg": alg, "error": repr(e)})
+        os.unlink(path)
+        for alg in (1, 3):
+            rows.append(ours(A, alg))
+        results[case] = rows
+        prods = rows[-1]["products"]
+        print(f"== {case}: n={A.shape[0]} nnzA={A.nnz} products={prods}")
+        for r in rows:
+            if "error" in r:
+                print(f"   {r['impl']:9s} alg{r['alg']}  ERROR {r['error']}")
+            else:
+                print(f"   {r['impl']:9s} alg{r['alg']}  {r['ms_median']:10.3f} ms  {2 * prods / r['ms_median'] / 1e6:9.1f} GFLOP/s  "
+                      f"peak beyond inputs {r['peak_bytes_excl_inputs'] / 2**20:10.1f} MiB  nnzC={r['nnzC']}")
+        sys.stdout.flush()
+    if args.out:
+        with open(args.out, "w") as f:
+            json.dump(results, f, indent=1)
+
+
+if __name__ == "__main__":
+    main()
