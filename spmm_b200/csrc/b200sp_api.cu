@@ -600,23 +600,27 @@ int run_spmv(b200sp_context *h, int m, int n, int64_t nnz, int64_t ncols, const 
   const T b = beta ? *(const T *)beta : T(0);
   cudaStream_t st = h->stream;
   if (m == 0 || ncols == 0) return B200SP_OK;
-  const char *mode = getenv("B200SP_SPMV_KERNEL");  // "vector" forces the row-group kernel
+  const char *mode = getenv("B200SP_SPMV_KERNEL");  // "vector" forces the row-group kernel, "tile" the merge-path one
   const bool want_stream = !(mode && strcmp(mode, "vector") == 0);
   if (want_stream && ncols == 1 && nnz > 0) {
     const int ntiles = (int)((nnz + SPMV_TILE - 1) / SPMV_TILE);
-    const size_t o_c = align_up((size_t)ntiles * sizeof(SpmvTileInfo), 256);
-    const size_t o_t = o_c + align_up((size_t)ntiles * sizeof(T), 256);
-    TRY(ensure(h, h->ws2, o_t + (size_t)ntiles * sizeof(T)));
+    const size_t o_h = align_up((size_t)ntiles * sizeof(SpmvTileInfo), 256);
+    const size_t o_c = o_h + align_up((size_t)ntiles * sizeof(T), 256);
+    TRY(ensure(h, h->ws2, o_c + (size_t)ntiles * sizeof(T)));
     char *base = (char *)h->ws2.ptr;
     SpmvTileInfo *info = (SpmvTileInfo *)base;
-    T *carry = (T *)(base + o_c), *tail = (T *)(base + o_t);
+    T *head = (T *)(base + o_h), *carry = (T *)(base + o_c);
     const int vec_ok = (((uintptr_t)Aj | (uintptr_t)Ax) & 15) == 0;
-    const int egrid = std::max(1, std::min((m + 255) / 256, NUM_SMS * 8));
-    k_spmv_empty_rows<T><<<egrid, 256, 0, st>>>(m, Ap, Y, b);
-    TRY(check_launch(h, "k_spmv_empty_rows"));
-    k_spmv_stream<T><<<ntiles, SPMV_THREADS, 0, st>>>(m, (int)nnz, Ap, Aj, Ax, X, Y, a, b, info, carry, tail, vec_ok);
-    TRY(check_launch(h, "k_spmv_stream"));
-    k_spmv_fixup<T><<<(ntiles + 255) / 256, 256, 0, st>>>(ntiles, info, carry, tail, Y, a, b);
+    int per_sm = 0;  // persistent grid: every CTA owns a contiguous run of tiles
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spmv_tile<T>, SPMV_THREADS, 0) != cudaSuccess || per_sm < 1) {
+      cudaGetLastError();
+      per_sm = 2;
+    }
+    const int grid = std::max(1, std::min(ntiles, NUM_SMS * per_sm));
+    k_spmv_tile<T><<<grid, SPMV_THREADS, 0, st>>>(m, (int)nnz, ntiles, Ap, Aj, Ax, X, Y, a, b, info, head, carry, vec_ok);
+    TRY(check_launch(h, "k_spmv_tile"));
+    if (ntiles == 1) return B200SP_OK;  // no row can span tiles
+    k_spmv_fixup<T><<<(ntiles + 255) / 256, 256, 0, st>>>(ntiles, info, head, carry, Y, a, b);
     return check_launch(h, "k_spmv_fixup");
   }
   const double avg = (double)nnz / (double)m;

@@ -52,6 +52,14 @@ def matrices():
     S = sp.csr_matrix((rng.standard_normal(rows.size).astype(np.float32), (rows, cols)), shape=(m, n))
     S.sort_indices()
     out["skewed"] = S
+    # rows that begin and end exactly on the SpMV tile boundaries (4096 fp32 / 2048 fp64 nonzeros),
+    # with empty rows sitting on the boundaries and a row of 3 full tiles
+    lens = [4096, 0, 2048, 2048, 0, 0, 12288, 1, 4095, 0, 8192, 0]
+    rows = np.concatenate([np.full(L, i) for i, L in enumerate(lens)])
+    cols = np.concatenate([np.sort(rng.choice(20000, L, replace=False)) for L in lens])
+    T = sp.csr_matrix((rng.standard_normal(rows.size).astype(np.float32), (rows, cols)), shape=(len(lens), 20000))
+    T.sort_indices()
+    out["tile_aligned"] = T
     return out
 
 
@@ -66,7 +74,7 @@ def get(name):
 
 
 @pytest.mark.parametrize("kernel", ["stream", "vector"])
-@pytest.mark.parametrize("name", ["short_rows", "c2_like", "long_rows", "tiny", "skewed"])
+@pytest.mark.parametrize("name", ["short_rows", "c2_like", "long_rows", "tiny", "skewed", "tile_aligned"])
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 def test_spmv(b200, name, dtype, kernel, monkeypatch):
     monkeypatch.setenv("B200SP_SPMV_KERNEL", kernel)
