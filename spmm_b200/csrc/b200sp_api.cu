@@ -603,22 +603,20 @@ int run_spmv(b200sp_context *h, int m, int n, int64_t nnz, int64_t ncols, const 
   const char *mode = getenv("B200SP_SPMV_KERNEL");  // "vector" forces the row-group kernel, "tile" the merge-path one
   const bool want_stream = !(mode && strcmp(mode, "vector") == 0);
   if (want_stream && ncols == 1 && nnz > 0) {
-    const int ntiles = (int)((nnz + SPMV_TILE - 1) / SPMV_TILE);
-    const size_t o_h = align_up((size_t)ntiles * sizeof(SpmvTileInfo), 256);
+    const long long total = (long long)m + nnz;  // merge items: row-end markers + nonzeros
+    const int ntiles = (int)((total + SPMV_TILE - 1) / SPMV_TILE);
+    const size_t o_i = align_up((size_t)(ntiles + 1) * sizeof(int), 256);
+    const size_t o_h = o_i + align_up((size_t)ntiles * sizeof(SpmvTileInfo), 256);
     const size_t o_c = o_h + align_up((size_t)ntiles * sizeof(T), 256);
     TRY(ensure(h, h->ws2, o_c + (size_t)ntiles * sizeof(T)));
     char *base = (char *)h->ws2.ptr;
-    SpmvTileInfo *info = (SpmvTileInfo *)base;
+    int *tile_row = (int *)base;
+    SpmvTileInfo *info = (SpmvTileInfo *)(base + o_i);
     T *head = (T *)(base + o_h), *carry = (T *)(base + o_c);
-    const int vec_ok = (((uintptr_t)Aj | (uintptr_t)Ax) & 15) == 0;
-    int per_sm = 0;  // persistent grid: every CTA owns a contiguous run of tiles
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spmv_tile<T>, SPMV_THREADS, 0) != cudaSuccess || per_sm < 1) {
-      cudaGetLastError();
-      per_sm = 2;
-    }
-    const int grid = std::max(1, std::min(ntiles, NUM_SMS * per_sm));
-    k_spmv_tile<T><<<grid, SPMV_THREADS, 0, st>>>(m, (int)nnz, ntiles, Ap, Aj, Ax, X, Y, a, b, info, head, carry, vec_ok);
-    TRY(check_launch(h, "k_spmv_tile"));
+    k_spmv_partition<<<(ntiles + 1 + 7) / 8, 256, 0, st>>>(m, total, ntiles, Ap, tile_row);
+    TRY(check_launch(h, "k_spmv_partition"));
+    k_spmv_merge<T><<<ntiles, SPMV_THREADS, 0, st>>>(m, (int)nnz, tile_row, Ap, Aj, Ax, X, Y, a, b, info, head, carry);
+    TRY(check_launch(h, "k_spmv_merge"));
     if (ntiles == 1) return B200SP_OK;  // no row can span tiles
     k_spmv_fixup<T><<<(ntiles + 255) / 256, 256, 0, st>>>(ntiles, info, head, carry, Y, a, b);
     return check_launch(h, "k_spmv_fixup");

@@ -64,42 +64,50 @@ k_spmv_vector(int m, const int *__restrict__ Ap, const int *__restrict__ Aj,
   }
 }
 
-// ---- nnz-balanced "tile" kernel (merge-path decomposition) ------------------------------------
-// Each tile is SPMV_THREADS * ITEMS consecutive nonzeros regardless of the row structure (one
-// heavy row cannot serialise a warp); the tile owns every row that STARTS inside it, empty rows
-// included.  The part of a tile that belongs to a row begun in an earlier tile ("head") and a
-// row left open at the tile's end ("carry") become per-tile partials; k_spmv_fixup adds them
-// in tile order, so the result is run-to-run deterministic (no atomics).
+// ---- merge-path kernel ------------------------------------------------------------------------
+// The work list is the merge of the m row-end markers with the nnz nonzeros (m + nnz items);
+// every CTA takes SPMV_TILE consecutive items of it, so a tile holds at most SPMV_TILE nonzeros
+// AND at most SPMV_TILE rows whatever the row-length distribution: one heavy row cannot
+// serialise a warp, a stretch of empty rows cannot either.  k_spmv_partition finds the row
+// coordinate of every tile boundary (a 32-ary search per warp: 4 rounds for 2^20 rows); the main
+// kernel then knows its row range [i0, i1] and nonzero range [j0, j1) up front.
+// Rows completed in a tile are written by it; the piece of a row begun in an earlier tile
+// ("head") and the piece of a row left open at the tile's end ("carry") become per-tile partials
+// that k_spmv_fixup adds in tile order, so the result is run-to-run deterministic (no atomics).
 constexpr int SPMV_THREADS = 256;
-constexpr int SPMV_ITEMS = 8;                           // nonzeros per thread and tile
-constexpr int SPMV_TILE = SPMV_THREADS * SPMV_ITEMS;    // 2048
-constexpr int SPMV_WINDOW = 1024;                       // indptr entries staged per batch of rows
+constexpr int SPMV_ITEMS = 8;                           // merge items per thread
+constexpr int SPMV_TILE = SPMV_THREADS * SPMV_ITEMS;    // 2048 merge items per tile
 
 struct SpmvTileInfo {
   int head_row;    // row begun earlier whose entries open this tile, or -1
-  int head_open;   // 1 when that row continues past the end of this tile
-  int carry_row;   // row that starts in this tile and continues into the next, or -1
+  int head_open;   // 1 when that row is not completed in this tile either (the tile lies inside it)
+  int carry_row;   // row that starts in this tile and is not completed in it, or -1
   int pad;
 };
 
-// CTA-wide lower bound over the sorted int array a[0..len): first index whose value is >= key.
-// Every thread of the CTA must call it; `len` and `key` are CTA-uniform.  256-ary: 3 rounds of
-// one load + one barrier for 2^20 rows instead of the 20 dependent loads of a binary search.
-__device__ __forceinline__ int cta_lower_bound(const int *__restrict__ a, int len, int key) {
-  int lo = 0, hi = len;  // invariant: a[i] < key for i < lo, a[i] >= key for i >= hi
-  while (hi - lo > SPMV_THREADS) {
-    const int step = (hi - lo + SPMV_THREADS - 1) / SPMV_THREADS;
-    const long long idx = (long long)lo + (long long)(threadIdx.x + 1) * step - 1;
-    const int less = (idx < hi) && (__ldg(a + idx) < key);
-    const int cnt = __syncthreads_count(less);  // probes are monotone: the first cnt are < key
+// Rows completed before merge diagonal d: the first i with Ap[i+1] + i + 1 > d (that key is
+// strictly increasing in i).  One warp per diagonal, 32-ary search.
+__global__ void __launch_bounds__(256)
+k_spmv_partition(int m, long long total, int ntiles, const int *__restrict__ Ap, int *__restrict__ tile_row) {
+  const int lane = lane_id();
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;  // boundary index 0..ntiles
+  if (k > ntiles) return;
+  const long long d = min((long long)k * SPMV_TILE, total);
+  int lo = 0, hi = m;  // answer in [lo, hi]: rows < lo are completed, rows >= hi are not
+  while (hi - lo > 32) {
+    const int step = (hi - lo + 31) / 32;
+    const long long i = (long long)lo + (long long)(lane + 1) * step - 1;
+    const bool done = (i < hi) && ((long long)__ldg(Ap + i + 1) + i + 1 <= d);
+    const int cnt = __popc(__ballot_sync(FULL, done));  // monotone: the first cnt probes are completed
     const long long nlo = (long long)lo + (long long)cnt * step;
     const long long nhi = nlo + step - 1;
     lo = (int)nlo;
     hi = (int)(nhi < hi ? nhi : hi);
   }
-  const int idx = lo + threadIdx.x;
-  const int less = (idx < hi) && (__ldg(a + idx) < key);
-  return lo + __syncthreads_count(less);
+  const int i = lo + lane;
+  const bool done = (i < hi) && ((long long)__ldg(Ap + i + 1) + i + 1 <= d);
+  const int res = lo + __popc(__ballot_sync(FULL, done));
+  if (lane == 0) tile_row[k] = res;
 }
 
 template <typename T>
@@ -107,209 +115,128 @@ __device__ __forceinline__ void spmv_store(T *__restrict__ y, int r, T sum, T al
   y[r] = beta == T(0) ? alpha * sum : alpha * sum + beta * y[r];
 }
 
-// 128-bit streaming loads of one full tile: entry 4e+u of the tile lands in slot 4q+u,
-// e = q*THREADS + tid.
 template <typename T>
-__device__ __forceinline__ void spmv_load_tile(const int *__restrict__ Aj, const T *__restrict__ Ax,
-                                               int t0, int tid, int (&jj)[SPMV_ITEMS], T (&aa)[SPMV_ITEMS]) {
-#pragma unroll
-  for (int q = 0; q < SPMV_ITEMS / 4; ++q) {
-    const int e = q * SPMV_THREADS + tid;
-    const int4 j4 = __ldcs(reinterpret_cast<const int4 *>(Aj + t0) + e);
-    jj[4 * q + 0] = j4.x; jj[4 * q + 1] = j4.y; jj[4 * q + 2] = j4.z; jj[4 * q + 3] = j4.w;
-    if (sizeof(T) == 4) {
-      const float4 a4 = __ldcs(reinterpret_cast<const float4 *>(Ax + t0) + e);
-      aa[4 * q + 0] = (T)a4.x; aa[4 * q + 1] = (T)a4.y; aa[4 * q + 2] = (T)a4.z; aa[4 * q + 3] = (T)a4.w;
-    } else {
-      const double2 a0 = __ldcs(reinterpret_cast<const double2 *>(Ax + t0) + 2 * e);
-      const double2 a1 = __ldcs(reinterpret_cast<const double2 *>(Ax + t0) + 2 * e + 1);
-      aa[4 * q + 0] = (T)a0.x; aa[4 * q + 1] = (T)a0.y; aa[4 * q + 2] = (T)a1.x; aa[4 * q + 3] = (T)a1.y;
-    }
-  }
-}
-
-// Persistent CTAs: CTA c owns the contiguous tiles [c*ntiles/G, (c+1)*ntiles/G).  Only the first
-// tile needs the indptr search; after that r_begin(k+1) = r_end(k).  The rows of a tile are
-// walked in batches of SPMV_WINDOW indptr entries staged in shared memory (one batch for all but
-// hypersparse tiles), which both finds r_end and feeds the row reduction.
-// Software pipeline over tiles, so that the gather path keeps working while a tile is reduced:
-//   iteration k:  store products(k) to smem | request indptr window(k), x gathers(k+1),
-//                 A vectors(k+2) | barrier | reduce tile k from smem | barrier
-template <typename T>
-__global__ void __launch_bounds__(SPMV_THREADS, sizeof(T) == 4 ? 3 : 2)
-k_spmv_tile(int m, int nnz, int ntiles, const int *__restrict__ Ap, const int *__restrict__ Aj,
-            const T *__restrict__ Ax, const T *__restrict__ x, T *__restrict__ y, T alpha, T beta,
-            SpmvTileInfo *__restrict__ info, T *__restrict__ head_val, T *__restrict__ carry_val,
-            int vec_ok) {
-  constexpr int ITEMS = SPMV_ITEMS, TILE = SPMV_TILE;
-  constexpr int WPT = SPMV_WINDOW / SPMV_THREADS;  // window entries per thread
+__global__ void __launch_bounds__(SPMV_THREADS)
+k_spmv_merge(int m, int nnz, const int *__restrict__ tile_row, const int *__restrict__ Ap,
+             const int *__restrict__ Aj, const T *__restrict__ Ax, const T *__restrict__ x,
+             T *__restrict__ y, T alpha, T beta, SpmvTileInfo *__restrict__ info,
+             T *__restrict__ head_val, T *__restrict__ carry_val) {
   constexpr int NW = SPMV_THREADS / 32;
-  __shared__ __align__(16) T s_prod[TILE + 4];
-  __shared__ int s_ap[SPMV_WINDOW + 1];
+  __shared__ T s_prod[SPMV_TILE + 4];
+  __shared__ int s_ap[SPMV_TILE + 2];
   __shared__ T s_part[NW];
-  __shared__ int s_cnt[NW];
-  __shared__ int s_carry_row;
+  __shared__ int s_nlong;
+  __shared__ int s_long[SPMV_TILE / 32 + 1];  // rows of the tile longer than 32 entries
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int k0 = (int)((long long)ntiles * blockIdx.x / gridDim.x);
-  const int k1 = (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
-  if (k0 >= k1) return;
-  auto tile_full = [&](int k) { return vec_ok && k < k1 && (nnz - k * TILE >= TILE); };
-  int jj[ITEMS], jn[ITEMS];
-  T aa[ITEMS], an[ITEMS], pr[ITEMS], xg[ITEMS];
-  // prologue: products of tile k0 in pr, A vectors of tile k0+1 in jj/aa
-  if (tile_full(k0)) spmv_load_tile<T>(Aj, Ax, k0 * TILE, tid, jj, aa);
-  int r_begin = cta_lower_bound(Ap, m + 1, k0 * TILE);  // overlaps the loads above
-  if (tile_full(k0)) {
+  const int k = blockIdx.x;
+  const long long total = (long long)m + nnz;
+  const long long d0 = (long long)k * SPMV_TILE, d1 = min(d0 + SPMV_TILE, total);
+  const int i0 = __ldg(tile_row + k), i1 = __ldg(tile_row + k + 1);  // rows [i0, i1) are completed here
+  const int j0 = (int)(d0 - i0), j1 = (int)(d1 - i1);               // nonzeros [j0, j1) are consumed here
+  const int nz = j1 - j0, nrows = i1 - i0;
+  // all requests of the tile go out together: indptr of rows i0 .. i1 (+1), indices and values
+  int jj[SPMV_ITEMS];
+  T aa[SPMV_ITEMS];
+  int apw[SPMV_ITEMS];
 #pragma unroll
-    for (int u = 0; u < ITEMS; ++u) xg[u] = __ldg(x + jj[u]);
-#pragma unroll
-    for (int u = 0; u < ITEMS; ++u) pr[u] = aa[u] * xg[u];
+  for (int q = 0; q < SPMV_ITEMS; ++q) {
+    const int e = q * SPMV_THREADS + tid;
+    jj[q] = e < nz ? __ldcs(Aj + j0 + e) : -1;
+    aa[q] = e < nz ? __ldcs(Ax + j0 + e) : T(0);
+    apw[q] = __ldg(Ap + min(i0 + e, m));
   }
-  if (tile_full(k0 + 1)) spmv_load_tile<T>(Aj, Ax, (k0 + 1) * TILE, tid, jj, aa);
-
-  for (int k = k0; k < k1; ++k) {
-    const int t0 = k * TILE;
-    const int t1 = (nnz - t0 > TILE) ? t0 + TILE : nnz;
-    const bool last_tile = (t1 == nnz);
-    // products of this tile -> shared memory
-    if (tile_full(k)) {
+  if (tid < 2) s_ap[SPMV_TILE + tid] = __ldg(Ap + min(i0 + SPMV_TILE + tid, m));
+  if (tid == 0) s_nlong = 0;
 #pragma unroll
-      for (int q = 0; q < ITEMS / 4; ++q) {
-        const int e = q * SPMV_THREADS + tid;
+  for (int q = 0; q < SPMV_ITEMS; ++q) {
+    const int e = q * SPMV_THREADS + tid;
+    s_ap[e] = apw[q];
+    if (jj[q] >= 0) s_prod[e] = aa[q] * __ldg(x + jj[q]);
+  }
+  __syncthreads();
+  // rows: s_ap[t] = Ap[i0 + t].  Row i0 may have begun in an earlier tile (head); row i1 is the
+  // one left incomplete (its entries, if any, are [max(Ap[i1], j0), j1)).
+  const int p0 = s_ap[0];                     // Ap[i0] <= j0
+  const bool has_head = j0 > p0;              // row i0 started before this tile
+  const bool head_closed = has_head && nrows > 0;
+  const int open_b = max(s_ap[nrows], j0);    // first entry of the incomplete row inside the tile
+  const bool has_open = (i1 < m) && (j1 > open_b);
+  const bool open_is_head = has_open && nrows == 0 && has_head;  // the tile lies inside one row
+  // Warp-uniform helper: one warp sums s_prod[b, e) in a fixed order.
+  auto warp_sum_range = [&](int b, int e) {
+    T sum = T(0);
+    for (int q = b + lane; q < e; q += 32) sum += s_prod[q];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) s_prod[4 * e + u] = pr[4 * q + u];
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(FULL, sum, o);
+    return sum;
+  };
+  // completed rows t = 0 .. nrows-1 cover s_prod[max(Ap[i0+t], j0) - j0, Ap[i0+t+1] - j0)
+  if (nrows >= 64) {  // many rows: one thread per short row, long ones are queued for the warps
+    for (int t = tid; t < nrows; t += SPMV_THREADS) {
+      const int b = max(s_ap[t], j0) - j0, e = s_ap[t + 1] - j0;
+      if (e - b > 32) {
+        s_long[atomicAdd(&s_nlong, 1)] = t;
+        continue;
       }
-    } else {
-      for (int e = t0 + tid; e < t1; e += SPMV_THREADS) s_prod[e - t0] = __ldcs(Ax + e) * __ldg(x + __ldcs(Aj + e));
+      T sum = T(0);
+      for (int q = b; q < e; q += 4) {  // four loads in flight; the additions stay in order
+        const T v0 = s_prod[q];
+        const T v1 = q + 1 < e ? s_prod[q + 1] : T(0);
+        const T v2 = q + 2 < e ? s_prod[q + 2] : T(0);
+        const T v3 = q + 3 < e ? s_prod[q + 3] : T(0);
+        sum += v0; sum += v1; sum += v2; sum += v3;
+      }
+      if (t == 0 && has_head) head_val[k] = sum;
+      else spmv_store(y, i0 + t, sum, alpha, beta);
     }
-    if (tid == 0) s_carry_row = -1;
-    // requests: first indptr window of this tile, x gathers of the next, A vectors of the one after
-    int apw[WPT];
-#pragma unroll
-    for (int q = 0; q < WPT; ++q) apw[q] = __ldg(Ap + min(r_begin + q * SPMV_THREADS + tid, m));
-    int ap_last = (tid == 0) ? __ldg(Ap + min(r_begin + SPMV_WINDOW, m)) : 0;
-    const bool next_full = tile_full(k + 1), next2_full = tile_full(k + 2);
-    if (next_full) {
-#pragma unroll
-      for (int u = 0; u < ITEMS; ++u) xg[u] = __ldg(x + jj[u]);
+    __syncthreads();
+    const int nlong = s_nlong;
+    for (int q = w; q < nlong; q += NW) {
+      const int t = s_long[q];
+      const T sum = warp_sum_range(max(s_ap[t], j0) - j0, s_ap[t + 1] - j0);
+      if (lane == 0) {
+        if (t == 0 && has_head) head_val[k] = sum;
+        else spmv_store(y, i0 + t, sum, alpha, beta);
+      }
     }
-    if (next2_full) spmv_load_tile<T>(Aj, Ax, t0 + 2 * TILE, tid, jn, an);
-
-    int r = r_begin;  // first row of the current batch
-    int head_row = -1, head_open = 0;
-    for (bool first = true;; first = false) {
-      if (!first) {  // hypersparse tile: more than SPMV_WINDOW rows start here
-#pragma unroll
-        for (int q = 0; q < WPT; ++q) apw[q] = __ldg(Ap + min(r + q * SPMV_THREADS + tid, m));
-        ap_last = (tid == 0) ? __ldg(Ap + min(r + SPMV_WINDOW, m)) : 0;
+  } else {  // few rows: one warp per row
+    for (int t = w; t < nrows; t += NW) {
+      const T sum = warp_sum_range(max(s_ap[t], j0) - j0, s_ap[t + 1] - j0);
+      if (lane == 0) {
+        if (t == 0 && has_head) head_val[k] = sum;
+        else spmv_store(y, i0 + t, sum, alpha, beta);
       }
-      int below = 0;  // batch entries (rows r + i) that start before t1; Ap[m] = nnz >= t1 never counts
-#pragma unroll
-      for (int q = 0; q < WPT; ++q) {
-        s_ap[q * SPMV_THREADS + tid] = apw[q];
-        below += (apw[q] < t1);
-      }
-      if (tid == 0) s_ap[SPMV_WINDOW] = ap_last;
-      below = warp_sum(below);
-      if (lane == 0) s_cnt[w] = below;
-      __syncthreads();  // s_prod, s_ap, s_cnt visible
-      int nbelow = 0;
-#pragma unroll
-      for (int q = 0; q < NW; ++q) nbelow += s_cnt[q];
-      if (first) {
-        // head: entries [t0, h_end) continue row r_begin-1 (Ap[r_begin] >= t0, r_begin <= m)
-        const int p_begin = s_ap[0];
-        const int h_end = min(p_begin, t1);
-        if (h_end > t0) {  // CTA-uniform
-          T part = T(0);
-          const int hl = h_end - t0;
-          const int per = (hl + NW - 1) / NW;  // contiguous chunk per warp
-          const int cb = min(w * per, hl), ce = min(cb + per, hl);
-          for (int q = cb + lane; q < ce; q += 32) part += s_prod[q];
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(FULL, part, o);
-          if (lane == 0) s_part[w] = part;
-          __syncthreads();
-          if (tid == 0) {
-            T sum = T(0);
-#pragma unroll
-            for (int q = 0; q < NW; ++q) sum += s_part[q];
-            head_val[k] = sum;
-          }
-          head_row = r_begin - 1;
-          head_open = p_begin > t1;  // the whole tile lies inside that row
-        }
-      }
-      // rows of this batch that start in the tile (the last tile also owns trailing empty rows)
-      const int rows_here = last_tile ? min(SPMV_WINDOW, m - r) : nbelow;
-      if (rows_here >= 64) {  // many short rows: one thread per row
-        for (int i = tid; i < rows_here; i += SPMV_THREADS) {
-          const int nxt = s_ap[i + 1];
-          const int b = s_ap[i] - t0, e = min(nxt, t1) - t0;
-          T sum = T(0);
-          for (int q = b; q < e; q += 4) {  // four loads in flight; the additions stay in order
-            const T v0 = s_prod[q];
-            const T v1 = q + 1 < e ? s_prod[q + 1] : T(0);
-            const T v2 = q + 2 < e ? s_prod[q + 2] : T(0);
-            const T v3 = q + 3 < e ? s_prod[q + 3] : T(0);
-            sum += v0; sum += v1; sum += v2; sum += v3;
-          }
-          if (!last_tile && nxt > t1) {  // the one row left open at the end of the tile
-            carry_val[k] = sum;
-            s_carry_row = r + i;
-          } else {
-            spmv_store(y, r + i, sum, alpha, beta);
-          }
-        }
-      } else {  // few long rows: one warp per row
-        for (int i = w; i < rows_here; i += NW) {
-          const int nxt = s_ap[i + 1];
-          const int b = s_ap[i] - t0, e = min(nxt, t1) - t0;
-          T sum = T(0);
-          for (int q = b + lane; q < e; q += 32) sum += s_prod[q];
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(FULL, sum, o);
-          if (lane == 0) {
-            if (!last_tile && nxt > t1) {
-              carry_val[k] = sum;
-              s_carry_row = r + i;
-            } else {
-              spmv_store(y, r + i, sum, alpha, beta);
-            }
-          }
-        }
-      }
-      r += rows_here;
-      const bool done = last_tile ? (r >= m) : (nbelow < SPMV_WINDOW);
-      __syncthreads();  // s_ap / s_cnt / s_prod / s_carry_row settled
-      if (done) break;
     }
+  }
+  // the incomplete row: every warp sums a contiguous chunk, thread 0 adds the chunks in order
+  if (has_open) {  // CTA-uniform
+    const int ob = open_b - j0, ol = nz - ob;
+    const int per = (ol + NW - 1) / NW;
+    const int cb = ob + min(w * per, ol), ce = ob + min((w + 1) * per, ol);
+    const T part = warp_sum_range(cb, ce);
+    if (lane == 0) s_part[w] = part;
+    __syncthreads();
     if (tid == 0) {
-      SpmvTileInfo ti;
-      ti.head_row = head_row;
-      ti.head_open = head_open;
-      ti.carry_row = s_carry_row;
-      ti.pad = 0;
-      info[k] = ti;
-    }
-    r_begin = r;
-    if (next_full) {
+      T sum = T(0);
 #pragma unroll
-      for (int u = 0; u < ITEMS; ++u) pr[u] = aa[u] * xg[u];
+      for (int q = 0; q < NW; ++q) sum += s_part[q];
+      if (open_is_head) head_val[k] = sum;
+      else carry_val[k] = sum;
     }
-    if (next2_full) {
-#pragma unroll
-      for (int u = 0; u < ITEMS; ++u) {
-        jj[u] = jn[u];
-        aa[u] = an[u];
-      }
-    }
+  }
+  if (tid == 0) {
+    SpmvTileInfo ti;
+    ti.head_row = (head_closed || open_is_head) ? i0 : -1;
+    ti.head_open = open_is_head;
+    ti.carry_row = (has_open && !open_is_head) ? i1 : -1;
+    ti.pad = 0;
+    info[k] = ti;
   }
 }
 
-// One thread per tile: the tile in which a multi-tile row ENDS (head present, not open) adds the
-// partials of that row in tile order - the carry of the tile where it started, the heads of the
-// tiles it covered completely, its own head - and writes the row.
+// One thread per tile: the tile in which a multi-tile row is COMPLETED (head present, not open)
+// adds the partials of that row in tile order - the carry of the tile where it started, the
+// heads of the tiles that lie inside it, its own head - and writes the row.
 template <typename T>
 __global__ void __launch_bounds__(256)
 k_spmv_fixup(int ntiles, const SpmvTileInfo *__restrict__ info, const T *__restrict__ head_val,
@@ -318,7 +245,7 @@ k_spmv_fixup(int ntiles, const SpmvTileInfo *__restrict__ info, const T *__restr
   if (t >= ntiles) return;
   const SpmvTileInfo me = info[t];
   if (me.head_row < 0 || me.head_open) return;
-  int ta = t - 1;  // walk back over the tiles the row covers completely, to the tile where it starts
+  int ta = t - 1;  // walk back over the tiles inside the row, to the tile where it starts
   while (ta > 0 && info[ta].carry_row != me.head_row) --ta;
   T sum = carry_val[ta];
   for (int q = ta + 1; q <= t; ++q) sum += head_val[q];
