@@ -30,6 +30,7 @@ namespace {
 constexpr size_t SMEM_MAX = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100
 constexpr size_t SMEM_BITMAP_MAX = 200 * 1024;  // budget for an n-bit bitmap in shared memory
 constexpr size_t SMEM_DENSE_MAX = 208 * 1024;   // budget for an n-column dense accumulator
+constexpr int RANKBM_MAX_N = 32768;             // widest matrix for the bitmap-rank output of the warp bins
 
 struct Buffer {  // grow-only device buffer
   void *ptr = nullptr;
@@ -399,13 +400,19 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
   switch (bp.kind) {
     case NUM_GROUP8: {
       const size_t smem = 16 * (size_t)bp.S * (sizeof(T) + 4);
-      k_num_hash_group<8, T><<<(cnt + 15) / 16, 128, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+      k_num_hash_group<8, T, false><<<(cnt + 15) / 16, 128, smem, st>>>(rows, cnt, bp.S, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
       return check_launch(h, "k_num_hash_group<8>");
     }
     case NUM_WARP: {
+      if (p.n <= RANKBM_MAX_N) {  // few columns: bitmap rank instead of the in-row sort
+        const size_t smem = 4 * ((size_t)bp.S * (sizeof(T) + 4) + 2 * (size_t)((p.n + 31) / 32) * 4);
+        TRY(set_smem(h, k_num_hash_group<32, T, true>, smem));
+        k_num_hash_group<32, T, true><<<(cnt + 3) / 4, 128, smem, st>>>(rows, cnt, bp.S, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+        return check_launch(h, "k_num_hash_group<32,rank>");
+      }
       const size_t smem = 4 * (size_t)bp.S * (sizeof(T) + 4);
-      TRY(set_smem(h, k_num_hash_group<32, T>, smem));
-      k_num_hash_group<32, T><<<(cnt + 3) / 4, 128, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+      TRY(set_smem(h, k_num_hash_group<32, T, false>, smem));
+      k_num_hash_group<32, T, false><<<(cnt + 3) / 4, 128, smem, st>>>(rows, cnt, bp.S, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
       return check_launch(h, "k_num_hash_group<32>");
     }
     case NUM_CTA_HASH: {

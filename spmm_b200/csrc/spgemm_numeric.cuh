@@ -74,9 +74,13 @@ __device__ __forceinline__ void bitonic_sort(int *keys, T *vals, int P, int tid,
 // ---- group-of-G-lanes per row, hash accumulator of S slots per group ---------------------
 // G = 8,  S = 64   : rows of C with <= 32 entries (4 rows per warp), rank sort
 // G = 32, S = 256+ : rows of C with <= S/2 entries (warp per row), rank or bitonic sort
-template <int G, typename T>
+// RANKBM (G == 32, few columns): a per-warp bitmap over the n columns records the touched
+// columns; the rank of a column among the set bits IS its position in the sorted output row, so
+// the table is emitted straight to C without compaction or sort (the bitonic sort of a 512-entry
+// row costs ~10x the accumulation itself).
+template <int G, typename T, bool RANKBM>
 __global__ void __launch_bounds__(128)
-k_num_hash_group(const int *__restrict__ rows, int nrows, int S, const int *__restrict__ Ap,
+k_num_hash_group(const int *__restrict__ rows, int nrows, int S, int n, const int *__restrict__ Ap,
                  const int *__restrict__ Aj, const T *__restrict__ Ax,
                  const int *__restrict__ Bp, const int *__restrict__ Bj,
                  const T *__restrict__ Bx, const int *__restrict__ Cp, int *__restrict__ Cj,
@@ -96,6 +100,14 @@ k_num_hash_group(const int *__restrict__ rows, int nrows, int S, const int *__re
     keys[s] = EMPTY;
     vals[s] = T(0);
   }
+  const int nwords = (n + 31) >> 5;
+  unsigned *bm = nullptr;
+  int *pre = nullptr;
+  if (RANKBM) {
+    bm = reinterpret_cast<unsigned *>(smem_raw + (size_t)groups_per_block * S * (sizeof(T) + 4)) + (size_t)g * 2 * nwords;
+    pre = reinterpret_cast<int *>(bm + nwords);
+    for (int s = sub; s < nwords; s += G) bm[s] = 0u;
+  }
   __syncwarp();
   int a_begin = 0, a_end = 0;
   if (row >= 0) {
@@ -107,12 +119,41 @@ k_num_hash_group(const int *__restrict__ rows, int nrows, int S, const int *__re
     T v = T(0);
     if (act) {
       bool fresh;
-      slot = hash_insert(keys, mask, __ldg(Bj + bidx), fresh);
+      const int j = __ldg(Bj + bidx);
+      slot = hash_insert(keys, mask, j, fresh);
+      if (RANKBM && fresh) atomicOr(&bm[j >> 5], 1u << (j & 31));
       v = mul_rn(__ldg(Ax + aidx), __ldg(Bx + bidx));
     }
     __syncwarp();  // inserts of this step are visible before the accumulate
     ordered_add(vals, slot, uid_base + slot, act, v, mc);
   });
+  if (RANKBM) {
+    if (row < 0) return;  // G == 32: warp-uniform
+    const int out = __ldg(Cp + row);
+    int carry = 0;  // exclusive prefix of the per-word popcounts
+    for (int c = 0; c < nwords; c += 32) {
+      const int wi = c + sub;
+      const int cnt = wi < nwords ? __popc(bm[wi]) : 0;
+      int incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(FULL, incl, o);
+        if (sub >= o) incl += t;
+      }
+      if (wi < nwords) pre[wi] = carry + incl - cnt;
+      carry += __shfl_sync(FULL, incl, 31);
+    }
+    __syncwarp();
+    for (int s = sub; s < S; s += 32) {
+      const int k = keys[s];
+      if (k != EMPTY) {
+        const int r = pre[k >> 5] + __popc(bm[k >> 5] & ((1u << (k & 31)) - 1u));
+        Cj[out + r] = k;
+        Cx[out + r] = scale_out(alpha, vals[s]);
+      }
+    }
+    return;
+  }
   const int nnz = compact_table<G, T>(keys, vals, S);
   if (row < 0) return;
   const int out = __ldg(Cp + row);

@@ -213,24 +213,42 @@ constexpr int SCAN1_THREADS = 1024;
 constexpr int SCAN1_MAX_ITEMS = 64;
 __global__ void __launch_bounds__(SCAN1_THREADS, 1)
 k_scan_single(int *Cp, int m, BinLimits bl, Counters *ctr) {
-  __shared__ long long s_warp[33];
+  // warp w owns the contiguous rows [w*seg, (w+1)*seg), walked 32 at a time with coalesced
+  // accesses: pass 1 sums the segment (and builds the histogram), pass 2 writes the scan.
+  __shared__ long long s_wsum[32];
   __shared__ int s_hist[MAX_BINS];
+  const int lane = lane_id(), w = threadIdx.x >> 5;
   if (threadIdx.x < MAX_BINS) s_hist[threadIdx.x] = 0;
   __syncthreads();
-  const int per = (m + SCAN1_THREADS - 1) / SCAN1_THREADS;
-  const int b = threadIdx.x * per, e = min(b + per, m);
+  const int seg = (((m + 31) / 32) + 31) & ~31;
+  const int b = min(w * seg, m), e = min(b + seg, m);
   long long sum = 0;
-  for (int i = b; i < e; ++i) {
+  for (int i = b + lane; i < e; i += 32) {
     const int c = Cp[i];
     sum += c;
     if (c > 0) atomicAdd(&s_hist[classify(bl, c)], 1);
   }
-  long long total;
-  long long ex = block_exscan(sum, s_warp, &total);
-  for (int i = b; i < e; ++i) {
-    const int c = Cp[i];
-    Cp[i] = (int)ex;
-    ex += c;
+  sum = warp_sum(sum);
+  if (lane == 0) s_wsum[w] = sum;
+  __syncthreads();
+  long long total = 0, base = 0;
+#pragma unroll 1
+  for (int q = 0; q < 32; ++q) {
+    const long long v = s_wsum[q];
+    if (q < w) base += v;
+    total += v;
+  }
+  for (int i0 = b; i0 < e; i0 += 32) {
+    const int i = i0 + lane;
+    const int c = i < e ? Cp[i] : 0;
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(FULL, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (i < e) Cp[i] = (int)(base + incl - c);
+    base += __shfl_sync(FULL, incl, 31);
   }
   if (threadIdx.x == 0) {
     Cp[m] = (int)total;

@@ -57,7 +57,8 @@ def test_cli_matches_reference_driver(tmp_path, alg, n, d):
     out = _run(os.path.join(OURS, f"spgemm_from_txt_alg{alg}"), pa, pb, c_ours)
     assert out.startswith(f"[C++] ALG{alg} wrote {c_ours}_*") and f"rows={n}" in out
     out_ref = _run(ref_exe, pa, pb, c_ref)
-    assert out_ref.startswith(f"[C++] ALG{alg} wrote")
+    # the reference's alg2 driver prints "ALG3" in its banner (spgemm_from_txt_alg2.cu:228), so only the prefix is checked
+    assert out_ref.startswith("[C++] ALG") and f"rows={n}" in out_ref
     op, oj, ox = _load(c_ours)
     rp, rj, rx = _load(c_ref)
     assert np.array_equal(op, rp), "indptr differs from the reference driver"
