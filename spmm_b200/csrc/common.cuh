@@ -88,9 +88,14 @@ __device__ __forceinline__ int next_pow2(int v) {
 // bidx indexes Bj/Bx, aidx indexes Aj/Ax.  Step order == stream order, lane order == stream
 // order inside a step.
 // -------------------------------------------------------------------------------------
-template <int G, class F>
+// load(act, bidx, aidx) issues the global loads of one step and returns them by value (a small
+// struct of registers); use(act, loaded, may_conflict) consumes a step.  The loads of step s+1 are
+// issued before step s is consumed (one step of software prefetch), so the L2 latency of the
+// B gathers overlaps the hash/accumulate work instead of adding to every step.
+template <int G, class LoadF, class UseF>
 __device__ __forceinline__ void stream_products(int a_begin, int a_end, const int *__restrict__ Aj,
-                                                const int *__restrict__ Bp, F &&f) {
+                                                const int *__restrict__ Bp, LoadF &&load, UseF &&use) {
+  using V = decltype(load(true, 0, 0));
   const int lane = lane_id();
   const int sub = lane & (G - 1);
   for (int base = a_begin; __any_sync(FULL, base < a_end); base += G) {
@@ -114,6 +119,8 @@ __device__ __forceinline__ void stream_products(int a_begin, int a_end, const in
       const int cnt = min(32, a_end - base);
       row_mode = total >= 24 * cnt;  // average B row >= 24 entries (warp-uniform for G == 32)
     }
+    V cur;
+    bool cur_act = false, have = false;  // `have` is warp-uniform
     if (row_mode) {
       const int cnt = min(32, a_end - base);
       for (int q = 0; q < cnt; ++q) {
@@ -121,9 +128,15 @@ __device__ __forceinline__ void stream_products(int a_begin, int a_end, const in
         const int ql = __shfl_sync(FULL, len, q);
         for (int t0 = 0; t0 < ql; t0 += 32) {
           const int tt = t0 + lane;
-          f(tt < ql, qs + tt, base + q, false);
+          const bool act = tt < ql;
+          V nxt = load(act, qs + tt, base + q);
+          if (have) use(cur_act, cur, false);
+          cur = nxt;
+          cur_act = act;
+          have = true;
         }
       }
+      if (have) use(cur_act, cur, false);
     } else {
       for (int p0 = 0; __any_sync(FULL, p0 < total); p0 += G) {
         const int p = p0 + sub;
@@ -136,8 +149,13 @@ __device__ __forceinline__ void stream_products(int a_begin, int a_end, const in
         }
         const int qs = __shfl_sync(FULL, start, q, G);
         const int qe = __shfl_sync(FULL, excl, q, G);
-        f(act, qs + (p - qe), base + q, true);
+        V nxt = load(act, qs + (p - qe), base + q);
+        if (have) use(cur_act, cur, true);
+        cur = nxt;
+        cur_act = act;
+        have = true;
       }
+      if (have) use(cur_act, cur, true);
     }
   }
 }

@@ -114,19 +114,31 @@ k_num_hash_group(const int *__restrict__ rows, int nrows, int S, int n, const in
     a_begin = __ldg(Ap + row);
     a_end = __ldg(Ap + row + 1);
   }
-  stream_products<G>(a_begin, a_end, Aj, Bp, [&](bool act, int bidx, int aidx, bool mc) {
-    int slot = 0;
-    T v = T(0);
-    if (act) {
-      bool fresh;
-      const int j = __ldg(Bj + bidx);
-      slot = hash_insert(keys, mask, j, fresh);
-      if (RANKBM && fresh) atomicOr(&bm[j >> 5], 1u << (j & 31));
-      v = mul_rn(__ldg(Ax + aidx), __ldg(Bx + bidx));
-    }
-    __syncwarp();  // inserts of this step are visible before the accumulate
-    ordered_add(vals, slot, uid_base + slot, act, v, mc);
-  });
+  struct Loaded {
+    int j;
+    T a, b;
+  };
+  stream_products<G>(
+      a_begin, a_end, Aj, Bp,
+      [&](bool act, int bidx, int aidx) {
+        Loaded v;
+        v.j = act ? __ldg(Bj + bidx) : 0;
+        v.a = act ? __ldg(Ax + aidx) : T(0);
+        v.b = act ? __ldg(Bx + bidx) : T(0);
+        return v;
+      },
+      [&](bool act, const Loaded &ld, bool mc) {
+        int slot = 0;
+        T v = T(0);
+        if (act) {
+          bool fresh;
+          slot = hash_insert(keys, mask, ld.j, fresh);
+          if (RANKBM && fresh) atomicOr(&bm[ld.j >> 5], 1u << (ld.j & 31));
+          v = mul_rn(ld.a, ld.b);
+        }
+        __syncwarp();  // inserts of this step are visible before the accumulate
+        ordered_add(vals, slot, uid_base + slot, act, v, mc);
+      });
   if (RANKBM) {
     if (row < 0) return;  // G == 32: warp-uniform
     const int out = __ldg(Cp + row);

@@ -223,11 +223,22 @@ k_scan_single(int *Cp, int m, BinLimits bl, Counters *ctr) {
   const int seg = (((m + 31) / 32) + 31) & ~31;
   const int b = min(w * seg, m), e = min(b + seg, m);
   long long sum = 0;
-  for (int i = b + lane; i < e; i += 32) {
-    const int c = Cp[i];
-    sum += c;
-    if (c > 0) atomicAdd(&s_hist[classify(bl, c)], 1);
+  int mybin = 0;  // lane q accumulates the count of bin q (warp-aggregated: no same-address atomics)
+  for (int i0 = b; i0 < e; i0 += 128) {
+    int c[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) c[u] = (i0 + u * 32 + lane < e) ? Cp[i0 + u * 32 + lane] : 0;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      sum += c[u];
+      const int bin = c[u] > 0 ? classify(bl, c[u]) : -1;
+      for (int q = 0; q < bl.nbins; ++q) {
+        const int k = __popc(__ballot_sync(FULL, bin == q));
+        if (lane == q) mybin += k;
+      }
+    }
   }
+  if (lane < bl.nbins && mybin) atomicAdd(&s_hist[lane], mybin);
   sum = warp_sum(sum);
   if (lane == 0) s_wsum[w] = sum;
   __syncthreads();
@@ -238,17 +249,22 @@ k_scan_single(int *Cp, int m, BinLimits bl, Counters *ctr) {
     if (q < w) base += v;
     total += v;
   }
-  for (int i0 = b; i0 < e; i0 += 32) {
-    const int i = i0 + lane;
-    const int c = i < e ? Cp[i] : 0;
-    int incl = c;
+  for (int i0 = b; i0 < e; i0 += 128) {
+    int c[4];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(FULL, incl, o);
-      if (lane >= o) incl += t;
+    for (int u = 0; u < 4; ++u) c[u] = (i0 + u * 32 + lane < e) ? Cp[i0 + u * 32 + lane] : 0;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 32 + lane;
+      int incl = c[u];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(FULL, incl, o);
+        if (lane >= o) incl += t;
+      }
+      if (i < e) Cp[i] = (int)(base + incl - c[u]);
+      base += __shfl_sync(FULL, incl, 31);
     }
-    if (i < e) Cp[i] = (int)(base + incl - c);
-    base += __shfl_sync(FULL, incl, 31);
   }
   if (threadIdx.x == 0) {
     Cp[m] = (int)total;

@@ -33,13 +33,15 @@ k_sym_hash_group(const int *__restrict__ rows, int nrows, int S, const int *__re
     a_end = __ldg(Ap + row + 1);
   }
   int cnt = 0;
-  stream_products<G>(a_begin, a_end, Aj, Bp, [&](bool act, int bidx, int, bool) {
-    if (act) {
-      bool fresh;
-      hash_insert(keys, mask, __ldg(Bj + bidx), fresh);
-      cnt += fresh;
-    }
-  });
+  stream_products<G>(
+      a_begin, a_end, Aj, Bp, [&](bool act, int bidx, int) { return act ? __ldg(Bj + bidx) : 0; },
+      [&](bool act, int j, bool) {
+        if (act) {
+          bool fresh;
+          hash_insert(keys, mask, j, fresh);
+          cnt += fresh;
+        }
+      });
   cnt = group_sum<G>(cnt);
   if (row >= 0 && sub == 0) Cp[row] = cnt;
 }
