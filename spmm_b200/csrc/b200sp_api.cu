@@ -546,7 +546,7 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
     off += cnt;
   }
   // counts -> indptr
-  const bool small_scan = p.m <= SCAN1_THREADS * SCAN1_MAX_ITEMS;
+  const bool small_scan = p.m <= 4096;  // measured: one block beats the 3-kernel tiled scan only up to here
   if (small_scan) {  // also fills the numeric-bin histogram
     k_scan_single<<<1, SCAN1_THREADS, 0, st>>>(dCp, p.m, p.num_limits, ctr);
     TRY(check_launch(h, "k_scan_single"));
