@@ -134,7 +134,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.002)
 
     def start(self):
         if self.nv:
@@ -333,6 +333,10 @@ def run_ours(args):
     e2e_val = 2.0 * total_products / float(t_e2e.item()) / 1e9
     h2d = (pp.nbytes + pj.nbytes + px.nbytes) + (0 if world == 1 else B.indptr.nbytes + B.indices.nbytes + B.data.nbytes)
     d2h = cp_.nbytes + cj_.nbytes + cx_.nbytes
+    if world > 1:  # bytes of the whole job, like `value`
+        tb2 = torch.tensor([h2d, d2h], dtype=torch.int64, device=dev)
+        dist.all_reduce(tb2)
+        h2d, d2h = int(tb2[0].item()), int(tb2[1].item())
 
     if rank != 0:
         if world > 1:
