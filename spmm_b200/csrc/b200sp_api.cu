@@ -30,6 +30,7 @@ namespace {
 constexpr size_t SMEM_MAX = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100
 constexpr size_t SMEM_BITMAP_MAX = 200 * 1024;  // budget for an n-bit bitmap in shared memory
 constexpr size_t SMEM_DENSE_MAX = 208 * 1024;   // budget for an n-column dense accumulator
+constexpr int DENSE_BLOCKED_MAX_BLOCKS = 64;     // most column blocks k_num_dense_blocked may need
 constexpr int RANKBM_MAX_N = 32768;             // widest matrix for the bitmap-rank output of the warp bins
 
 struct Buffer {  // grow-only device buffer
@@ -38,7 +39,7 @@ struct Buffer {  // grow-only device buffer
 };
 
 enum SymKind { SYM_GROUP8, SYM_WARP, SYM_CTA_HASH, SYM_CTA_BITMAP };
-enum NumKind { NUM_GROUP8, NUM_WARP, NUM_CTA_HASH, NUM_GLOBAL, NUM_DENSE };
+enum NumKind { NUM_GROUP8, NUM_WARP, NUM_CTA_HASH, NUM_GLOBAL, NUM_DENSE, NUM_DENSE_BLOCKED };
 
 struct BinPlan {
   int kind;
@@ -58,6 +59,7 @@ struct Plan {
   int sym_count[MAX_BINS]{}, num_count[MAX_BINS]{};
   int *rows_sym = nullptr, *rows_num = nullptr;  // device, inside ws
   int64_t num_products = 0, nnzC = 0, max_row_products = 0;
+  bool b_canonical = true;  // B rows verified sorted (needed by the column-blocked dense kernel)
 };
 
 }  // namespace
@@ -336,6 +338,22 @@ void plan_bins(Plan &p) {
     p.num_limits.nbins = 4;
     for (int b = 0; b < 4; ++b) p.num_limits.limit[b] = dl[b];
     p.num_bins[3] = {NUM_DENSE, 0};
+  } else if ((size_t)p.n * 8 <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_DENSE_MAX) {
+    // wide matrix: rows with at least ~n/64 entries are worth an n-column sweep and go to the
+    // column-blocked dense kernel; the shared-memory hash kernels keep the rows below that
+    const int t_dense = std::max(512, std::min(12288, p.n / 64));
+    int nb = 3;
+    if (t_dense > 512) {
+      p.num_limits.limit[nb] = std::min(6144, t_dense);
+      p.num_bins[nb++] = {NUM_CTA_HASH, 8192};
+    }
+    if (t_dense > 6144) {
+      p.num_limits.limit[nb] = t_dense;
+      p.num_bins[nb++] = {NUM_CTA_HASH, 16384};
+    }
+    p.num_limits.limit[nb] = INT_MAX;
+    p.num_bins[nb++] = {NUM_DENSE_BLOCKED, 0};
+    p.num_limits.nbins = nb;
   }
 }
 
@@ -430,7 +448,22 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         k_num_dense_cta<T><<<persistent_grid(cnt, smem + 4352), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
         return check_launch(h, "k_num_dense_cta");
       }
-      // fp64 with n between the fp32 and fp64 budgets: fall through to the global kernel
+      // fp64 with n between the fp32 and fp64 budgets: column blocks
+    case NUM_DENSE_BLOCKED:
+      if (p.b_canonical && (size_t)p.n * sizeof(T) <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_DENSE_MAX) {
+        // up to 4 blocks: half-SM blocks (2 CTAs of 256 threads per SM); wider: full-SM blocks, 512 threads
+        const bool half = (size_t)p.n * sizeof(T) <= 4 * (SMEM_DENSE_MAX / 2);
+        const size_t budget = half ? SMEM_DENSE_MAX / 2 : SMEM_DENSE_MAX;
+        const int nblk = (int)(((size_t)p.n * sizeof(T) + budget - 1) / budget);
+        const int W = (((p.n + nblk - 1) / nblk) + 31) & ~31;
+        const size_t smem = (size_t)W * sizeof(T);
+        const int nt = half ? 256 : 512;
+        TRY(set_smem(h, k_num_dense_blocked<T>, smem));
+        const int grid = std::max(1, std::min(cnt, NUM_SMS * (half ? 2 : 1)));
+        k_num_dense_blocked<T><<<grid, nt, smem, st>>>(rows, cnt, p.n, W, nblk, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+        return check_launch(h, "k_num_dense_blocked");
+      }
+      // B not canonical (or absurdly wide): the global-memory kernel takes any input
     case NUM_GLOBAL: {
       const size_t bytes = (size_t)((p.n + 31) / 32) * 8;  // bitmap + prefix
       int grid = std::max(1, std::min(cnt, 2 * NUM_SMS / p.num_chunks));
@@ -564,12 +597,21 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
   }
   k_scatter_rows<true><<<sgrid, 256, 0, st>>>(p.m, dCp, p.num_limits, ctr, p.rows_num);
   TRY(check_launch(h, "k_scatter_rows<num>"));
+  // the column-blocked dense kernel relies on sorted B rows: verify (O(nnzB) reads) before using it
+  const bool need_canonical = p.num_bins[p.num_limits.nbins - 1].kind == NUM_DENSE_BLOCKED ||
+                              (p.num_bins[p.num_limits.nbins - 1].kind == NUM_DENSE);
+  if (need_canonical && nnzB > 0) {
+    const int cgrid = std::max(1, std::min((int)((k + 7) / 8), NUM_SMS * 8));
+    k_csr_check_canonical<<<cgrid, 256, 0, st>>>(p.k, p.n, dBp, dBj, &ctr->b_bad);
+    TRY(check_launch(h, "k_csr_check_canonical"));
+  }
   cudaEventRecord(h->ev[1], st);
   // sync #2: nnz(C) + numeric bin sizes (the reference's cusparseSpMatGetSize sync)
   CUDA_TRY(h, cudaMemcpyAsync(h->h_counters, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(h, cudaStreamSynchronize(st));
   cudaEventElapsedTime(&h->ms_symbolic, h->ev[0], h->ev[1]);
   p.nnzC = (int64_t)h->h_counters->nnz_c;
+  p.b_canonical = !h->h_counters->b_bad;
   for (int b = 0; b < p.num_limits.nbins; ++b) p.num_count[b] = h->h_counters->num_count[b];
   *nnzC = p.nnzC;
   if (p.nnzC > INT32_MAX)

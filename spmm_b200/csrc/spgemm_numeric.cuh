@@ -507,4 +507,118 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
   }
 }
 
+// ---- CTA per row, dense accumulator over one COLUMN BLOCK at a time --------------------------
+// For matrices too wide for k_num_dense_cta (n * sizeof(T) > shared memory) and rows of C with
+// many entries: the n columns are cut into nblk blocks of W columns; for each block the CTA
+// walks the A row once, applies - in A-row order, one barrier per B row, as above - only the
+// part of every B row that falls into the block (B rows are sorted, so that part is one
+// segment, found by two binary searches while the chunk of A nonzeros is staged), then sweeps
+// the W accumulators in order.  Blocks are processed left to right, so the row's output is
+// simply appended block after block: sorted, no hash, no sort, no global-memory accumulator.
+// Work per row = nblk * nnz(A_i) searches + products + n sweep steps; used for rows whose nnz
+// makes the n-column sweep worthwhile (host: plan_bins).  Requires canonical B.
+template <typename T>
+__global__ void __launch_bounds__(512, 1)
+k_num_dense_blocked(const int *__restrict__ rows, int nrows, int n, int W, int nblk,
+                    const int *__restrict__ Ap, const int *__restrict__ Aj, const T *__restrict__ Ax,
+                    const int *__restrict__ Bp, const int *__restrict__ Bj, const T *__restrict__ Bx,
+                    const int *__restrict__ Cp, int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int2 s_seg[512];  // {start, len} of the staged B-row segments
+  __shared__ T s_a[512];
+  __shared__ int s_wcnt[16];
+  T *acc = reinterpret_cast<T *>(smem_raw);
+  const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
+  const T UNT = Untouched<T>::value();
+  for (int c = tid; c < W; c += NT) acc[c] = UNT;
+  const int cpw = ((W + nw - 1) / nw + 31) & ~31;  // columns per warp in the sweep, a multiple of 32
+  __syncthreads();
+  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
+    const int row = rows[ridx];
+    const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
+    int out = __ldg(Cp + row);
+    for (int cb = 0; cb < nblk; ++cb) {
+      const int c0 = cb * W, c1 = min(n, c0 + W);
+      for (int base = a_begin; base < a_end; base += NT) {
+        const int t = base + tid;
+        int2 sg = make_int2(0, 0);
+        T av = T(0);
+        if (t < a_end) {
+          const int kk = __ldg(Aj + t);
+          int lo = __ldg(Bp + kk), hi = __ldg(Bp + kk + 1);
+          if (nblk > 1 && hi > lo) {
+            const int e = hi;
+            if (c0 > 0) {  // first entry with column >= c0
+              while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (__ldg(Bj + mid) < c0) lo = mid + 1;
+                else hi = mid;
+              }
+            }
+            hi = e;
+            if (c1 < n) {  // first entry with column >= c1
+              int l2 = lo;
+              while (l2 < hi) {
+                const int mid = (l2 + hi) >> 1;
+                if (__ldg(Bj + mid) < c1) l2 = mid + 1;
+                else hi = mid;
+              }
+            }
+          }
+          sg = make_int2(lo, hi - lo);
+          av = __ldg(Ax + t);
+        }
+        s_seg[tid] = sg;
+        s_a[tid] = av;
+        __syncthreads();
+        const int cnt = min(NT, a_end - base);
+        for (int q = 0; q < cnt; ++q) {
+          const int2 g = s_seg[q];
+          if (g.y == 0) continue;  // CTA-uniform
+          const T a = s_a[q];
+          for (int u = tid; u < g.y; u += NT) {
+            const int j = __ldg(Bj + g.x + u) - c0;
+            const T cur = acc[j];
+            acc[j] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, mul_rn(a, __ldg(Bx + g.x + u)));
+          }
+          __syncthreads();
+        }
+        __syncthreads();
+      }
+      // sweep of the block: warp w owns columns [w*cpw, (w+1)*cpw) of it
+      const int wl = min(w * cpw, c1 - c0), wh = min(wl + cpw, c1 - c0);
+      int mine = 0;
+      for (int c = wl; c < wh; c += 32) {
+        const bool touched = (c + lane < wh) && !Untouched<T>::is(acc[c + lane]);
+        mine += __popc(__ballot_sync(FULL, touched));
+      }
+      if (lane == 0) s_wcnt[w] = mine;
+      __syncthreads();
+      int pos = out, tot = 0;
+      for (int q = 0; q < nw; ++q) {
+        const int v = s_wcnt[q];
+        if (q < w) pos += v;
+        tot += v;
+      }
+      if (mine) {  // warp-uniform
+        for (int c = wl; c < wh; c += 32) {
+          T v = UNT;
+          if (c + lane < wh) v = acc[c + lane];
+          const bool touched = !Untouched<T>::is(v);
+          const unsigned bal = __ballot_sync(FULL, touched);
+          if (touched) {
+            const int o = pos + __popc(bal & ((1u << lane) - 1u));
+            Cj[o] = c0 + c + lane;
+            Cx[o] = scale_out(alpha, v);
+            acc[c + lane] = UNT;
+          }
+          pos += __popc(bal);
+        }
+      }
+      out += tot;
+      __syncthreads();
+    }
+  }
+}
+
 }  // namespace b200sp

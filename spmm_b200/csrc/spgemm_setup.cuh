@@ -29,6 +29,7 @@ struct Counters {
   unsigned long long nnz_c;
   int max_row_products;
   int overflow;  // a row's product count did not fit int32
+  int b_bad;     // B is not canonical (unsorted row / index out of range): no column-blocked kernel
   int sym_count[MAX_BINS];
   int sym_cursor[MAX_BINS];
   int num_count[MAX_BINS];
