@@ -30,6 +30,7 @@ namespace {
 constexpr size_t SMEM_MAX = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100
 constexpr size_t SMEM_BITMAP_MAX = 200 * 1024;  // budget for an n-bit bitmap in shared memory
 constexpr size_t SMEM_DENSE_MAX = 208 * 1024;   // budget for an n-column dense accumulator
+constexpr size_t SMEM_BLOCKED_MAX = 176 * 1024;  // accumulator budget of k_num_dense_blocked (it has ~46 KB of static smem)
 constexpr int DENSE_BLOCKED_MAX_BLOCKS = 64;     // most column blocks k_num_dense_blocked may need
 constexpr int RANKBM_MAX_N = 32768;             // widest matrix for the bitmap-rank output of the warp bins
 
@@ -60,6 +61,7 @@ struct Plan {
   int *rows_sym = nullptr, *rows_num = nullptr;  // device, inside ws
   int64_t num_products = 0, nnzC = 0, max_row_products = 0;
   bool b_canonical = true;  // B rows verified sorted (needed by the column-blocked dense kernel)
+  int bounds_nblk = 0, bounds_W = 0;  // geometry of the per-B-row block-boundary table now in ws3 (0 = none)
 };
 
 }  // namespace
@@ -72,6 +74,7 @@ struct b200sp_context {
   void *alloc_ctx = nullptr;
   Buffer ws;       // plan workspace (row lists, counters, scan tiles)
   Buffer ws2;      // global bitmap workspace of the heavy-row kernels
+  Buffer ws3;      // per-B-row column-block boundaries of k_num_dense_blocked
   Buffer io[10];   // device staging of the *_host entry points
   void *pinned_out[3] = {nullptr, nullptr, nullptr};  // host staging of C (handle owned)
   size_t pinned_out_size[3] = {0, 0, 0};
@@ -227,6 +230,7 @@ extern "C" int b200sp_release_workspace(b200sp_handle_t h) {
   cudaStreamSynchronize(h->stream);
   release(h, h->ws);
   release(h, h->ws2);
+  release(h, h->ws3);
   for (auto &b : h->io) release(h, b);
   h->plan.valid = false;
   return B200SP_OK;
@@ -338,7 +342,7 @@ void plan_bins(Plan &p) {
     p.num_limits.nbins = 4;
     for (int b = 0; b < 4; ++b) p.num_limits.limit[b] = dl[b];
     p.num_bins[3] = {NUM_DENSE, 0};
-  } else if ((size_t)p.n * 8 <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_DENSE_MAX) {
+  } else if ((size_t)p.n * 8 <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_BLOCKED_MAX) {
     // wide matrix: rows with at least ~n/64 entries are worth an n-column sweep and go to the
     // column-blocked dense kernel; the shared-memory hash kernels keep the rows below that
     const int t_dense = std::max(512, std::min(12288, p.n / 64));
@@ -450,17 +454,23 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       }
       // fp64 with n between the fp32 and fp64 budgets: column blocks
     case NUM_DENSE_BLOCKED:
-      if (p.b_canonical && (size_t)p.n * sizeof(T) <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_DENSE_MAX) {
-        // up to 4 blocks: half-SM blocks (2 CTAs of 256 threads per SM); wider: full-SM blocks, 512 threads
-        const bool half = (size_t)p.n * sizeof(T) <= 4 * (SMEM_DENSE_MAX / 2);
-        const size_t budget = half ? SMEM_DENSE_MAX / 2 : SMEM_DENSE_MAX;
+      if (p.b_canonical && (size_t)p.n * sizeof(T) <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_BLOCKED_MAX) {
+        const size_t budget = SMEM_BLOCKED_MAX;  // one CTA of 512 threads per SM
         const int nblk = (int)(((size_t)p.n * sizeof(T) + budget - 1) / budget);
         const int W = (((p.n + nblk - 1) / nblk) + 31) & ~31;
         const size_t smem = (size_t)W * sizeof(T);
-        const int nt = half ? 256 : 512;
+        if (p.bounds_nblk != nblk || p.bounds_W != W) {  // first numeric call of this plan / value type
+          const size_t total = (size_t)p.k * (nblk + 1);
+          TRY(ensure(h, h->ws3, total * sizeof(int)));
+          const int bgrid = (int)std::max<size_t>(1, std::min<size_t>((total + 255) / 256, (size_t)NUM_SMS * 16));
+          k_block_bounds<<<bgrid, 256, 0, st>>>(p.k, nblk, W, p.Bp, p.Bj, (int *)h->ws3.ptr);
+          TRY(check_launch(h, "k_block_bounds"));
+          p.bounds_nblk = nblk;
+          p.bounds_W = W;
+        }
         TRY(set_smem(h, k_num_dense_blocked<T>, smem));
-        const int grid = std::max(1, std::min(cnt, NUM_SMS * (half ? 2 : 1)));
-        k_num_dense_blocked<T><<<grid, nt, smem, st>>>(rows, cnt, p.n, W, nblk, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+        const int grid = std::max(1, std::min(cnt, NUM_SMS));
+        k_num_dense_blocked<T><<<grid, BLOCKED_NT, smem, st>>>(rows, cnt, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
         return check_launch(h, "k_num_dense_blocked");
       }
       // B not canonical (or absurdly wide): the global-memory kernel takes any input
@@ -518,6 +528,7 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
   p.alg = alg;
   p.num_chunks = chunked ? (int)std::min<double>(64.0, std::ceil(1.0 / (double)chunk_fraction - 1e-6)) : 1;
   p.num_products = 0; p.nnzC = 0; p.max_row_products = 0;
+  p.bounds_nblk = p.bounds_W = 0;
   memset(p.sym_count, 0, sizeof p.sym_count);
   memset(p.num_count, 0, sizeof p.num_count);
   plan_bins(p);

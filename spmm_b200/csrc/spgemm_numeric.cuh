@@ -510,28 +510,66 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
 // ---- CTA per row, dense accumulator over one COLUMN BLOCK at a time --------------------------
 // For matrices too wide for k_num_dense_cta (n * sizeof(T) > shared memory) and rows of C with
 // many entries: the n columns are cut into nblk blocks of W columns; for each block the CTA
-// walks the A row once, applies - in A-row order, one barrier per B row, as above - only the
-// part of every B row that falls into the block (B rows are sorted, so that part is one
-// segment, found by two binary searches while the chunk of A nonzeros is staged), then sweeps
-// the W accumulators in order.  Blocks are processed left to right, so the row's output is
-// simply appended block after block: sorted, no hash, no sort, no global-memory accumulator.
-// Work per row = nblk * nnz(A_i) searches + products + n sweep steps; used for rows whose nnz
-// makes the n-column sweep worthwhile (host: plan_bins).  Requires canonical B.
+// walks the A row once and applies only the part of every B row that falls into the block (B
+// rows are sorted, so that part is one segment, found by binary search while a chunk of A
+// nonzeros is staged), then sweeps the W accumulators in order.  Blocks are processed left to
+// right, so the row's output is simply appended block after block: sorted, no hash table, no
+// sort, no global-memory accumulator.
+// Power-law inputs have thousands of SHORT segments per row, so the barrier-per-B-row scheme of
+// k_num_dense_cta would idle: instead the staged segments are flattened into one product stream
+// (prefix sum of the segment lengths, load-balanced search) that the CTA consumes NT products
+// per round.  Order per column is kept by a claim table: every pending product does
+// atomicMin(claim[hash(col)], q) with q its position in the A row; after a barrier only the
+// products that hold the minimum of their slot are applied (equal q means the same B row,
+// hence distinct columns), the others retry in the next sub-round.  Collisions are rare, so a
+// round costs ~2 barriers for NT products whatever the segment lengths.
+// Requires canonical B (the host checks).
+// bounds[kk*(nblk+1) + b] = first entry of B row kk with column >= b*W (b = 0..nblk; the last is
+// the row end): the segment of row kk inside column block b is [bounds[..b], bounds[..b+1]).
+// Built once per plan and value type; k*(nblk+1) ints of workspace.
+__global__ void __launch_bounds__(256)
+k_block_bounds(int k, int nblk, int W, const int *__restrict__ Bp, const int *__restrict__ Bj,
+               int *__restrict__ bounds) {
+  const long long total = (long long)k * (nblk + 1);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int kk = (int)(i / (nblk + 1)), b = (int)(i % (nblk + 1));
+    int lo = __ldg(Bp + kk), hi = __ldg(Bp + kk + 1);
+    if (b == nblk) lo = hi;
+    else if (b > 0) {
+      const int key = b * W;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(Bj + mid) < key) lo = mid + 1;
+        else hi = mid;
+      }
+    }
+    bounds[i] = lo;
+  }
+}
+
+constexpr int BLOCKED_NT = 512;
+constexpr int BLOCKED_CLAIM = 8192;  // claim slots (power of two)
+
 template <typename T>
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(BLOCKED_NT, 1)
 k_num_dense_blocked(const int *__restrict__ rows, int nrows, int n, int W, int nblk,
                     const int *__restrict__ Ap, const int *__restrict__ Aj, const T *__restrict__ Ax,
-                    const int *__restrict__ Bp, const int *__restrict__ Bj, const T *__restrict__ Bx,
+                    const int *__restrict__ bounds, const int *__restrict__ Bj, const T *__restrict__ Bx,
                     const int *__restrict__ Cp, int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
+  constexpr int NT = BLOCKED_NT, NWARP = NT / 32;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ int2 s_seg[512];  // {start, len} of the staged B-row segments
-  __shared__ T s_a[512];
-  __shared__ int s_wcnt[16];
+  __shared__ int2 s_seg[NT];      // {start, len} of the staged B-row segments
+  __shared__ T s_a[NT];           // their A values
+  __shared__ int s_pre[NT + 1];   // exclusive prefix of the segment lengths
+  __shared__ int s_claim[BLOCKED_CLAIM];
+  __shared__ int s_wcnt[NWARP];
   T *acc = reinterpret_cast<T *>(smem_raw);
-  const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
+  const int tid = threadIdx.x, lane = lane_id(), w = tid >> 5;
   const T UNT = Untouched<T>::value();
   for (int c = tid; c < W; c += NT) acc[c] = UNT;
-  const int cpw = ((W + nw - 1) / nw + 31) & ~31;  // columns per warp in the sweep, a multiple of 32
+  for (int c = tid; c < BLOCKED_CLAIM; c += NT) s_claim[c] = INT_MAX;
+  const int cpw = ((W + NWARP - 1) / NWARP + 31) & ~31;  // columns per warp in the sweep
   __syncthreads();
   for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
     const int row = rows[ridx];
@@ -540,52 +578,77 @@ k_num_dense_blocked(const int *__restrict__ rows, int nrows, int n, int W, int n
     for (int cb = 0; cb < nblk; ++cb) {
       const int c0 = cb * W, c1 = min(n, c0 + W);
       for (int base = a_begin; base < a_end; base += NT) {
+        // ---- stage up to NT A nonzeros: the segment of their B row inside [c0, c1) ----
         const int t = base + tid;
         int2 sg = make_int2(0, 0);
         T av = T(0);
         if (t < a_end) {
           const int kk = __ldg(Aj + t);
-          int lo = __ldg(Bp + kk), hi = __ldg(Bp + kk + 1);
-          if (nblk > 1 && hi > lo) {
-            const int e = hi;
-            if (c0 > 0) {  // first entry with column >= c0
-              while (lo < hi) {
-                const int mid = (lo + hi) >> 1;
-                if (__ldg(Bj + mid) < c0) lo = mid + 1;
-                else hi = mid;
-              }
-            }
-            hi = e;
-            if (c1 < n) {  // first entry with column >= c1
-              int l2 = lo;
-              while (l2 < hi) {
-                const int mid = (l2 + hi) >> 1;
-                if (__ldg(Bj + mid) < c1) l2 = mid + 1;
-                else hi = mid;
-              }
-            }
-          }
+          const int *bd = bounds + (size_t)kk * (nblk + 1) + cb;
+          const int lo = __ldg(bd), hi = __ldg(bd + 1);
           sg = make_int2(lo, hi - lo);
           av = __ldg(Ax + t);
         }
         s_seg[tid] = sg;
         s_a[tid] = av;
-        __syncthreads();
-        const int cnt = min(NT, a_end - base);
-        for (int q = 0; q < cnt; ++q) {
-          const int2 g = s_seg[q];
-          if (g.y == 0) continue;  // CTA-uniform
-          const T a = s_a[q];
-          for (int u = tid; u < g.y; u += NT) {
-            const int j = __ldg(Bj + g.x + u) - c0;
-            const T cur = acc[j];
-            acc[j] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, mul_rn(a, __ldg(Bx + g.x + u)));
-          }
-          __syncthreads();
+        // exclusive prefix of the lengths
+        int incl = sg.y;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int v = __shfl_up_sync(FULL, incl, o);
+          if (lane >= o) incl += v;
         }
+        if (lane == 31) s_wcnt[w] = incl;
         __syncthreads();
+        int wbase = 0;
+        for (int q = 0; q < w; ++q) wbase += s_wcnt[q];
+        s_pre[tid + 1] = wbase + incl;
+        if (tid == 0) s_pre[0] = 0;
+        __syncthreads();
+        const int total = s_pre[NT];
+        // ---- consume the product stream, NT products per round; the loads of round r+1 are
+        //      issued before round r is resolved ----
+        int q = 0, j = 0;
+        T bval = T(0), aval = T(0);
+        bool have = false;
+        auto fetch = [&](int e) {  // locate product e of the stream and request its column / value
+          have = e < total;
+          if (have) {
+            int lo = 0, hi = NT;  // largest q with s_pre[q] <= e
+            while (hi - lo > 1) {
+              const int mid = (lo + hi) >> 1;
+              if (s_pre[mid] <= e) lo = mid;
+              else hi = mid;
+            }
+            q = lo;
+            const int idx = s_seg[q].x + (e - s_pre[q]);
+            j = __ldg(Bj + idx);
+            bval = __ldg(Bx + idx);
+            aval = s_a[q];
+          }
+        };
+        fetch(tid);
+        for (int r0 = 0; r0 < total; r0 += NT) {
+          bool pending = have;
+          const int myq = q, myj = j - c0;
+          const T p = mul_rn(aval, bval);
+          const int slot = (int)(((unsigned)myj * 0x9E3779B1u) >> 19) & (BLOCKED_CLAIM - 1);
+          fetch(r0 + NT + tid);
+          while (true) {
+            if (pending) atomicMin(&s_claim[slot], myq);
+            __syncthreads();
+            if (pending && s_claim[slot] == myq) {
+              const T cur = acc[myj];
+              acc[myj] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, p);
+              pending = false;
+              s_claim[slot] = INT_MAX;
+            }
+            if (__syncthreads_count(pending) == 0) break;
+          }
+        }
+        __syncthreads();  // s_seg / s_a / s_pre are restaged
       }
-      // sweep of the block: warp w owns columns [w*cpw, (w+1)*cpw) of it
+      // ---- sweep of the block: warp w owns columns [w*cpw, (w+1)*cpw) of it ----
       const int wl = min(w * cpw, c1 - c0), wh = min(wl + cpw, c1 - c0);
       int mine = 0;
       for (int c = wl; c < wh; c += 32) {
@@ -595,7 +658,7 @@ k_num_dense_blocked(const int *__restrict__ rows, int nrows, int n, int W, int n
       if (lane == 0) s_wcnt[w] = mine;
       __syncthreads();
       int pos = out, tot = 0;
-      for (int q = 0; q < nw; ++q) {
+      for (int q = 0; q < NWARP; ++q) {
         const int v = s_wcnt[q];
         if (q < w) pos += v;
         tot += v;
