@@ -50,15 +50,57 @@ def slice_rows(Ap, Aj, Ax, r0, r1):
 
 
 def concat_panels(panels):
-    """Concatenate C row panels [(indptr, indices, data), ...] with the indptr offset fix-up."""
+    """Concatenate C row panels [(indptr, indices, data), ...] with the indptr offset fix-up.
+    The result's indptr is int32 when nnz(C) fits, int64 otherwise (a single CSR with more than
+    2^31-1 entries cannot have an int32 indptr; the panels themselves always do)."""
     ptrs, off = [np.zeros(1, dtype=np.int64)], 0
     for p, _, _ in panels:
         ptrs.append(np.asarray(p[1:], dtype=np.int64) + off)
         off += int(p[-1])
-    if off > np.iinfo(np.int32).max:
-        raise OverflowError("nnz(C) does not fit int32 indptr")
-    return (np.concatenate(ptrs).astype(np.int32), np.concatenate([j for _, j, _ in panels]),
-            np.concatenate([x for _, _, x in panels]))
+    ptr = np.concatenate(ptrs)
+    if off <= np.iinfo(np.int32).max:
+        ptr = ptr.astype(np.int32)
+    return (ptr, np.concatenate([j for _, j, _ in panels]), np.concatenate([x for _, _, x in panels]))
+
+
+def split_rows_by_bound(row_prods, n_cols, r0, r1, limit=(1 << 31) - 1):
+    """Cut rows [r0, r1) into consecutive sub-panels whose nnz(C) cannot exceed `limit`:
+    nnz(C_i) <= min(products_i, n_cols), so the running sum of that bound decides the cuts.
+    Returns the list of boundaries [r0, ..., r1].  A single row always fits (bound <= n_cols)."""
+    ub = np.minimum(np.asarray(row_prods[r0:r1], dtype=np.int64), int(n_cols))
+    csum = np.cumsum(ub)
+    bounds, base = [r0], 0
+    while bounds[-1] < r1:
+        # last row index whose inclusive running bound stays within base + limit
+        k = int(np.searchsorted(csum, base + limit, side="right"))
+        k = max(k, bounds[-1] - r0 + 1)  # always take at least one row
+        k = min(k, r1 - r0)
+        bounds.append(r0 + k)
+        base = int(csum[k - 1])
+    return bounds
+
+
+def spgemm_panels(A, b_dev, shape, r0=0, r1=None, limit=(1 << 31) - 1, alg=0, chunk_fraction=0.2, alpha=1.0,
+                  row_prods=None):
+    """Generator over the C sub-panels of rows [r0, r1) of A @ B on the current GPU.
+
+    A: host CSR triple; b_dev: device csr_matrix of B; yields (p0, p1, c_dev) with c_dev a device
+    csr_matrix of rows [p0, p1).  Every sub-panel has fewer than `limit` entries (int32 indptr),
+    so a product with more than 2^31-1 nonzeros - R-MAT scale >= 20 squared - streams through one
+    GPU panel by panel; the consumer decides what to keep (D2H, checksum, ...)."""
+    from . import cusparse
+    from .sparse import csr_matrix
+    m, k, n = shape
+    r1 = m if r1 is None else r1
+    Ap, Aj, Ax = A
+    if row_prods is None:
+        row_prods = row_products(Ap, Aj, b_dev.indptr.cpu().numpy())
+    cuts = split_rows_by_bound(row_prods, n, r0, r1, limit)
+    for p0, p1 in zip(cuts[:-1], cuts[1:]):
+        pp, pj, px = slice_rows(Ap, Aj, Ax, p0, p1)
+        a = csr_matrix((np.ascontiguousarray(px), np.ascontiguousarray(pj), pp), shape=(p1 - p0, k))
+        a._canonical = True
+        yield p0, p1, cusparse.spgemm(a, b_dev, alpha=alpha, alg=alg, chunk_fraction=chunk_fraction)
 
 
 # ------------------------------------------------------------------- B broadcast ----------

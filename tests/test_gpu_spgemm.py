@@ -180,3 +180,19 @@ def test_numeric_reuse_new_values(b200):
     A2.data = (A.data * np.float32(3.0)).astype(np.float32)
     want = oracle_spgemm(A2, B)
     assert_csr_bitwise((c.indptr.cpu().numpy(), cj.cpu().numpy(), cx.cpu().numpy()), want, "reuse")
+
+
+def test_streamed_sub_panels(b200):
+    """Products with more entries than an int32 indptr can address stream through the GPU in
+    row sub-panels (multi.spgemm_panels); here the limit is lowered so that many panels form."""
+    from spmm_b200 import multi
+    A, B = helpers.skewed_pair()
+    b = b200.csr_matrix(B)
+    want = helpers.oracle_spgemm(A, B, nthreads=0)
+    panels, seen = [], 0
+    for p0, p1, c in multi.spgemm_panels(helpers.triple(A), b, (A.shape[0], A.shape[1], B.shape[1]), limit=60000):
+        assert p0 == seen and c.shape[0] == p1 - p0 and (c.nnz <= 60000 or p1 - p0 == 1)
+        seen = p1
+        panels.append((c.indptr.cpu().numpy(), c.indices.cpu().numpy(), c.data.cpu().numpy()))
+    assert seen == A.shape[0] and len(panels) >= 5
+    helpers.assert_csr_bitwise(multi.concat_panels(panels), want, "streamed panels")

@@ -105,3 +105,15 @@ def test_row_panels_world2_gloo():
     (a0, a1, n0), (b0, b1, n1) = res[0][1], res[1][1]
     assert a0 == 0 and a1 == b0 and b1 == A.shape[0] and 0 < a1 < A.shape[0]
     assert int(n0) + int(n1) == C.nnz
+
+
+def test_split_rows_by_bound():
+    rp = np.array([5, 100, 3, 0, 50, 7, 7, 7])
+    assert multi.split_rows_by_bound(rp, 60, 0, 8, limit=70) == [0, 4, 7, 8]
+    assert multi.split_rows_by_bound(rp, 60, 2, 8, limit=1000) == [2, 8]
+    # a limit below one row's bound still makes progress, one row per panel
+    assert multi.split_rows_by_bound(rp, 60, 0, 8, limit=10) == [0, 1, 2, 4, 5, 6, 7, 8]
+    cuts = multi.split_rows_by_bound(rp, 60, 0, 8, limit=70)
+    ub = np.minimum(rp, 60)
+    assert all(ub[a:b].sum() <= 70 for a, b in zip(cuts[:-1], cuts[1:]))
+    assert multi.split_rows_by_bound(rp, 60, 3, 3) == [3]
