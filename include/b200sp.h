@@ -175,6 +175,58 @@ int b200sp_csr_is_canonical(b200sp_handle_t handle, int64_t m, int64_t ncols, co
 int b200sp_csr_sort_indices(b200sp_handle_t handle, int dtype, int64_t m, int64_t nnz,
                             const int32_t *dAp, int32_t *dAj, void *dAx);
 
+/* ------------------------------------- format conversion and canonicalisation ---- */
+/*   All arrays are device pointers; int32 indices, base 0.  Scratch
+ * (~24.3 bytes per entry) comes from the handle's workspace.  Every call synchronises once. */
+
+/* COO -> canonical CSR: entries sorted by (row, column), duplicates summed.  Duplicates are
+ * added sequentially in INPUT order with separately rounded adds (deterministic; the reference
+ * uses floating-point atomics).  dCp has m+1 entries; dCj/dCx need room for nnz entries, of
+ * which *nnz_out (host) are written.  Replaces coo_matrix.sum_duplicates + tocsr
+ * (cupyx/scipy/sparse/_coo.py:356-459, 517-540; cupyx/cusparse.py coosort :908-955,
+ * coo2csr :957-970).  B200SP_ERR_INVALID for a coordinate outside [0,m) x [0,n). */
+int b200sp_coo_to_csr(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t nnz,
+                      const int32_t *dRow, const int32_t *dCol, const void *dVal, int32_t *dCp,
+                      int32_t *dCj, void *dCx, int64_t *nnz_out);
+
+/* CSR with unsorted rows and/or duplicate entries -> canonical CSR (out of place), same summation
+ * rule.  Replaces csr_matrix.sum_duplicates (cupyx/scipy/sparse/_compressed.py:971-991). */
+int b200sp_csr_sum_duplicates(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t nnz,
+                              const int32_t *dAp, const int32_t *dAj, const void *dAx,
+                              int32_t *dCp, int32_t *dCj, void *dCx, int64_t *nnz_out);
+
+/* CSC (n+1 column pointers, row indices) of an m x n matrix -> CSR with sorted rows; entries are
+ * only re-ordered (nnz is preserved, duplicates stay adjacent in input order).  Replaces
+ * csc_matrix.tocsr (cupyx/scipy/sparse/_csc.py:304-326; cupyx/cusparse.py csc2csr :1092-1114). */
+int b200sp_csc_to_csr(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t nnz,
+                      const int32_t *dColPtr, const int32_t *dRowIdx, const void *dVal,
+                      int32_t *dCp, int32_t *dCj, void *dCx);
+
+/* CSR of an m x n matrix -> CSC (equivalently: the CSR of the transpose).  Replaces
+ * csr_matrix.tocsc / .T (cupyx/scipy/sparse/_csr.py:455-477; cupyx/cusparse.py csr2csc :1014-1036). */
+int b200sp_csr_to_csc(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t nnz,
+                      const int32_t *dAp, const int32_t *dAj, const void *dAx, int32_t *dColPtr,
+                      int32_t *dRowIdx, void *dVal);
+
+/* ------------------------------------------------ dense image and comparison ---- */
+/*  */
+
+#define B200SP_ORDER_ROW 0 /* C order: out[i * n + j] */
+#define B200SP_ORDER_COL 1 /* F order: out[i + j * m] */
+
+/* CSR -> dense m x n array (zero-filled first; duplicates accumulate in storage order).
+ * Replaces csr_matrix.toarray (cupyx/scipy/sparse/_csr.py:383-420; cusparse.csr2dense :768-798). */
+int b200sp_csr_to_dense(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, const int32_t *dAp,
+                        const int32_t *dAj, const void *dAx, void *dOut, int order);
+
+/* max |A - B| over all positions of two canonical CSR matrices with m rows (an entry stored in
+ * only one of them is compared with 0); NaN if any compared value is NaN.  The fused form of
+ * `abs(C.toarray() - D.toarray()).max()` (numerical_error/error.py:25-29) without the two
+ * m x n dense arrays.  *result is a host double. */
+int b200sp_csr_max_abs_diff(b200sp_handle_t handle, int dtype, int64_t m, const int32_t *dAp,
+                            const int32_t *dAj, const void *dAx, const int32_t *dBp,
+                            const int32_t *dBj, const void *dBx, double *result);
+
 /* ----------------------------------------------------------- statistics ---- */
 
 #define B200SP_MAX_BINS 16

@@ -126,3 +126,68 @@ def is_canonical(Ap, Aj, ncols):
     Ap, Aj = _i32(Ap), _i32(Aj)
     return bool(lib().oracle_csr_is_canonical(ctypes.c_int64(len(Ap) - 1), ctypes.c_int64(ncols),
                                               _p(Ap, _i32p), _p(Aj, _i32p)))
+
+
+# ---- format conversions (convert_oracle.c) ------------------------------------------------
+
+def _fp(dt):
+    return (ctypes.c_float, ctypes.POINTER(ctypes.c_float), "f32") if dt == np.float32 else \
+        (ctypes.c_double, ctypes.POINTER(ctypes.c_double), "f64")
+
+
+def coo_to_csr(row, col, val, shape):
+    """Canonical CSR of a COO triple: sorted by (row, col), duplicates summed in input order."""
+    row, col = _i32(row), _i32(col)
+    dt = np.dtype(val.dtype)
+    val = np.ascontiguousarray(val, dtype=dt)
+    m, n = shape
+    _, vp, sfx = _fp(dt)
+    Cp = np.zeros(m + 1, dtype=np.int32)
+    Cj = np.empty(len(row), dtype=np.int32)
+    Cx = np.empty(len(row), dtype=dt)
+    fn = getattr(lib(), "oracle_coo_to_csr_" + sfx)
+    fn.restype = ctypes.c_int64
+    k = fn(ctypes.c_int64(m), ctypes.c_int64(n), ctypes.c_int64(len(row)), _p(row, _i32p), _p(col, _i32p),
+           _p(val, vp), _p(Cp, _i32p), _p(Cj, _i32p), _p(Cx, vp))
+    if k < 0:
+        raise ValueError("coordinate out of range" if k == -1 else "oracle OOM")
+    return Cp, Cj[:k].copy(), Cx[:k].copy()
+
+
+def csr_sum_duplicates(A, shape):
+    """Canonical form of a CSR with unsorted rows / duplicates (same summation rule)."""
+    Ap, Aj, Ax = A
+    row = np.repeat(np.arange(shape[0], dtype=np.int32), np.diff(Ap))
+    return coo_to_csr(row, Aj, Ax, shape)
+
+
+def transpose_compressed(ptr, idx, val, nminor):
+    """(ptr, idx, val) compressed along the other axis (csr_tocsc restated): CSC -> CSR with
+    nminor = number of rows, or CSR -> CSC with nminor = number of columns."""
+    ptr, idx = _i32(ptr), _i32(idx)
+    dt = np.dtype(val.dtype)
+    val = np.ascontiguousarray(val, dtype=dt)
+    _, vp, sfx = _fp(dt)
+    optr = np.zeros(nminor + 1, dtype=np.int32)
+    oidx = np.empty(len(idx), dtype=np.int32)
+    oval = np.empty(len(idx), dtype=dt)
+    fn = getattr(lib(), "oracle_transpose_" + sfx)
+    fn.restype = ctypes.c_int
+    rc = fn(ctypes.c_int64(len(ptr) - 1), ctypes.c_int64(nminor), _p(ptr, _i32p), _p(idx, _i32p), _p(val, vp),
+            _p(optr, _i32p), _p(oidx, _i32p), _p(oval, vp))
+    if rc:
+        raise ValueError("index out of range")
+    return optr, oidx, oval
+
+
+def csr_max_abs_diff(A, B):
+    Ap, Aj, Ax = A
+    Bp, Bj, Bx = B
+    dt = np.dtype(Ax.dtype)
+    _, vp, sfx = _fp(dt)
+    fn = getattr(lib(), "oracle_csr_max_abs_diff_" + sfx)
+    fn.restype = ctypes.c_double
+    Ap, Aj, Bp, Bj = _i32(Ap), _i32(Aj), _i32(Bp), _i32(Bj)
+    Ax, Bx = np.ascontiguousarray(Ax, dtype=dt), np.ascontiguousarray(Bx, dtype=dt)
+    return float(fn(ctypes.c_int64(len(Ap) - 1), _p(Ap, _i32p), _p(Aj, _i32p), _p(Ax, vp), _p(Bp, _i32p),
+                    _p(Bj, _i32p), _p(Bx, vp)))

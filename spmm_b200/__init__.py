@@ -14,6 +14,6 @@ from . import _lib
 _lib.load()
 
 from . import cusparse, host, sparse  # noqa: E402
-from .sparse import csr_matrix  # noqa: E402
+from .sparse import coo_matrix, csc_matrix, csr_matrix, max_abs_diff  # noqa: E402
 
-__all__ = ["cusparse", "sparse", "host", "csr_matrix"]
+__all__ = ["cusparse", "sparse", "host", "csr_matrix", "csc_matrix", "coo_matrix", "max_abs_diff"]

@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libb200sp.so")
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_OVERFLOW, ERR_STATE, ERR_IO = -1, -2, -3, -4, -5, -6
 R_32F, R_64F = 0, 1
+ORDER_ROW, ORDER_COL = 0, 1
 MAX_BINS = 16
 
 c_i64 = ctypes.c_int64
@@ -57,6 +58,15 @@ SYMBOLS = [
      [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     ("b200sp_csr_is_canonical", ctypes.c_int, [c_vp, c_i64, c_i64, c_vp, c_vp, ctypes.POINTER(ctypes.c_int)]),
     ("b200sp_csr_sort_indices", ctypes.c_int, [c_vp, ctypes.c_int, c_i64, c_i64, c_vp, c_vp, c_vp]),
+    ("b200sp_coo_to_csr", ctypes.c_int,
+     [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, i64p]),
+    ("b200sp_csr_sum_duplicates", ctypes.c_int,
+     [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, i64p]),
+    ("b200sp_csc_to_csr", ctypes.c_int, [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    ("b200sp_csr_to_csc", ctypes.c_int, [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    ("b200sp_csr_to_dense", ctypes.c_int, [c_vp, ctypes.c_int, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, ctypes.c_int]),
+    ("b200sp_csr_max_abs_diff", ctypes.c_int,
+     [c_vp, ctypes.c_int, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.POINTER(ctypes.c_double)]),
     ("b200sp_get_stats", ctypes.c_int, [c_vp, ctypes.POINTER(Stats)]),
     ("b200sp_reset_stats", ctypes.c_int, [c_vp]),
     ("b200sp_read_csr_txt", ctypes.c_int,

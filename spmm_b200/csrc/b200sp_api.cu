@@ -22,6 +22,7 @@
 #include "spgemm_symbolic.cuh"
 #include "spmv.cuh"
 #include "csr_utils.cuh"
+#include "convert.cuh"
 
 using namespace b200sp;
 
@@ -772,6 +773,10 @@ extern "C" int b200sp_csr_sort_indices(b200sp_handle_t h, int dtype, int64_t m, 
   if (too_long) return fail(h, B200SP_ERR_INVALID, "csr_sort_indices: an unsorted row has more than %d entries", cap);
   return B200SP_OK;
 }
+
+// ===================================== canonicalisation, dense, compare ====
+
+#include "convert_api.inl"
 
 // ================================================================= host-buffer one-shots ====
 

@@ -35,6 +35,10 @@ def _check_dtype(dt):
     return dt
 
 
+def _rtype(dt):
+    return _lib.R_32F if np.dtype(dt) == np.float32 else _lib.R_64F
+
+
 def _bind_stream(h, dev):
     _lib.check(h, _lib.load().b200sp_set_stream(h, ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
 
@@ -53,6 +57,8 @@ class csr_matrix:
     def __init__(self, arg1, shape=None, dtype=None, copy=False):
         dev = _device()
         self._canonical = None
+        if isinstance(arg1, _via_csr):  # csr_matrix(coo) / csr_matrix(csc): convert on the device
+            arg1 = arg1.tocsr()
         if isinstance(arg1, csr_matrix):
             self.data = arg1.data.clone() if copy else arg1.data
             self.indices = arg1.indices.clone() if copy else arg1.indices
@@ -136,13 +142,22 @@ class csr_matrix:
         self._canonical = None
 
     def sum_duplicates(self):
-        """No-op for canonical matrices (every matrix the reference's profilers build is);
-        duplicate summation is a "next" row and is refused loudly."""
+        """Sorted rows without duplicate entries, in place (_compressed.py:971-991).  No-op for
+        canonical matrices (every matrix the reference's profilers build is); otherwise the rows
+        are sorted and duplicates summed in storage order (b200sp_csr_sum_duplicates)."""
         if self.has_canonical_format:
             return
-        self.sort_indices()
-        if not self.has_canonical_format:
-            raise NotImplementedError("sum_duplicates on a matrix with duplicate entries is not built yet")
+        m, n = self.shape
+        cp = torch.empty(m + 1, dtype=torch.int32, device=self.device)
+        cj = torch.empty(self.nnz, dtype=torch.int32, device=self.device)
+        cx = torch.empty(self.nnz, dtype=self.data.dtype, device=self.device)
+        out = ctypes.c_int64(0)
+        h = self._handle()
+        _lib.check(h, _lib.load().b200sp_csr_sum_duplicates(
+            h, _rtype(self.dtype), m, n, self.nnz, self.indptr.data_ptr(), self.indices.data_ptr(),
+            self.data.data_ptr(), cp.data_ptr(), cj.data_ptr(), cx.data_ptr(), ctypes.byref(out)))
+        self.indptr, self.indices, self.data = cp, cj[:out.value].clone(), cx[:out.value].clone()
+        self._canonical = True
 
     # -- transfers --------------------------------------------------------------------------
     def get(self):
@@ -150,14 +165,55 @@ class csr_matrix:
         return sp.csr_matrix((self.data.cpu().numpy(), self.indices.cpu().numpy(), self.indptr.cpu().numpy()),
                              shape=self.shape)
 
-    def toarray(self):
-        """Dense torch tensor (used by the numerical_error checks, numerical_error/error.py:27)."""
-        out = torch.zeros(self.shape, dtype=self.data.dtype, device=self.device)
-        if self.nnz:
-            counts = (self.indptr[1:] - self.indptr[:-1]).long()
-            rows = torch.repeat_interleave(torch.arange(self.shape[0], device=self.device), counts)
-            out.index_put_((rows, self.indices.long()), self.data, accumulate=True)
-        return out
+    def toarray(self, order=None):
+        """Dense torch tensor with the same values (_csr.py:383-420; used by the numerical_error
+        checks, numerical_error/error.py:27).  order 'C' (default) or 'F'."""
+        order = "C" if order is None else order.upper()
+        if order not in ("C", "F"):
+            raise ValueError("order not understood")
+        m, n = self.shape
+        buf = torch.empty(m * n, dtype=self.data.dtype, device=self.device)
+        if m * n:
+            h = self._handle()
+            _lib.check(h, _lib.load().b200sp_csr_to_dense(
+                h, _rtype(self.dtype), m, n, self.indptr.data_ptr(), self.indices.data_ptr(), self.data.data_ptr(),
+                buf.data_ptr(), _lib.ORDER_ROW if order == "C" else _lib.ORDER_COL))
+        return buf.view(m, n) if order == "C" else buf.view(n, m).t()
+
+    def _transposed_arrays(self):
+        """(ptr, idx, val) of the CSC form = the CSR of the transpose (b200sp_csr_to_csc)."""
+        m, n = self.shape
+        ptr = torch.empty(n + 1, dtype=torch.int32, device=self.device)
+        idx = torch.empty(self.nnz, dtype=torch.int32, device=self.device)
+        val = torch.empty(self.nnz, dtype=self.data.dtype, device=self.device)
+        h = self._handle()
+        _lib.check(h, _lib.load().b200sp_csr_to_csc(
+            h, _rtype(self.dtype), m, n, self.nnz, self.indptr.data_ptr(), self.indices.data_ptr(),
+            self.data.data_ptr(), ptr.data_ptr(), idx.data_ptr(), val.data_ptr()))
+        return ptr, idx, val
+
+    def tocsc(self, copy=False):
+        """_csr.py:455-477 (cusparse.csr2csc)."""
+        ptr, idx, val = self._transposed_arrays()
+        return csc_matrix((val, idx, ptr), shape=self.shape)
+
+    def tocoo(self, copy=False):
+        """_csr.py:433-453: row indices expanded from indptr."""
+        counts = (self.indptr[1:] - self.indptr[:-1]).long()
+        row = torch.repeat_interleave(torch.arange(self.shape[0], dtype=torch.int32, device=self.device), counts)
+        return coo_matrix((self.data.clone() if copy else self.data, (row, self.indices)), shape=self.shape)
+
+    def transpose(self, axes=None, copy=False):
+        """_csr.py:512-540: the CSR of the transpose (the reference returns the CSC view of the
+        same arrays; here the arrays are re-ordered so that the result can feed spgemm)."""
+        if axes is not None:
+            raise ValueError("swapping dimensions is the only logical permutation")
+        ptr, idx, val = self._transposed_arrays()
+        return csr_matrix((val, idx, ptr), shape=(self.shape[1], self.shape[0]))
+
+    @property
+    def T(self):
+        return self.transpose()
 
     def tocsr(self, copy=False):
         return self.copy() if copy else self
@@ -183,6 +239,8 @@ class csr_matrix:
             out = csr_matrix((self.data * other, self.indices, self.indptr), shape=self.shape)
             out._canonical = self._canonical
             return out
+        if isinstance(other, (csc_matrix, coo_matrix)):  # _csr.py:161-164: convert, then spgemm
+            return self * other.tocsr()
         if hasattr(other, "tocsr") and hasattr(other, "nnz"):  # scipy matrix: upload, then spgemm
             return self * csr_matrix(other)
         if isinstance(other, np.ndarray):
@@ -204,5 +262,201 @@ class csr_matrix:
     dot = __mul__
 
 
+class _via_csr:
+    """Behaviour shared by the non-CSR containers: every product converts to CSR first, as the
+    reference does on CUDA 12 (_csc.py:120-127 `self.tocsr()` -> spgemm; _base.py:105-134)."""
+    ndim = 2
+
+    @property
+    def shape(self):
+        return self._shape
+
+    @property
+    def dtype(self):
+        return _NP_DT[self.data.dtype]
+
+    @property
+    def nnz(self):
+        return int(self.data.numel())
+
+    @property
+    def device(self):
+        return self.data.device
+
+    def _handle(self):
+        h = _lib.handle(self.device.index)
+        _bind_stream(h, self.device)
+        return h
+
+    def __mul__(self, other):
+        return self.tocsr().__mul__(other)
+
+    def __matmul__(self, other):
+        if np.isscalar(other):
+            raise ValueError("Scalar operands are not allowed, use '*' instead")
+        return self.tocsr().__mul__(other)
+
+    dot = __mul__
+
+    def toarray(self, order=None):
+        return self.tocsr().toarray(order)
+
+    def get(self):
+        return self.tocsr().get().asformat(self.format)
+
+
+class coo_matrix(_via_csr):
+    """Device COO container (mirror of cupyx.scipy.sparse.coo_matrix, _coo.py): `.row/.col/.data`,
+    built from a SciPy matrix or `(data, (row, col))`; `tocsr()` sorts by (row, col) and sums
+    duplicates on the device (_coo.py:356-459, 517-540)."""
+    format = "coo"
+
+    def __init__(self, arg1, shape=None, dtype=None, copy=False):
+        dev = _device()
+        if hasattr(arg1, "tocoo") and hasattr(arg1, "nnz") and not isinstance(arg1, (csr_matrix, _via_csr)):
+            c = arg1.tocoo()
+            dt = _check_dtype(dtype or c.dtype)
+            self.data = _to_dev(c.data.astype(dt, copy=False), _TORCH_DT[dt], dev)
+            self.row = _to_dev(c.row.astype(np.int32, copy=False), torch.int32, dev)
+            self.col = _to_dev(c.col.astype(np.int32, copy=False), torch.int32, dev)
+            self._shape = tuple(int(v) for v in c.shape)
+        elif isinstance(arg1, tuple) and len(arg1) == 2 and isinstance(arg1[1], tuple):
+            data, (row, col) = arg1
+            if isinstance(data, torch.Tensor):
+                dt = _check_dtype(dtype or _NP_DT.get(data.dtype, None) or np.float32)
+            else:
+                dt = _check_dtype(dtype or np.asarray(data).dtype)
+            self.data = _to_dev(data, _TORCH_DT[dt], dev)
+            self.row = _to_dev(row, torch.int32, dev)
+            self.col = _to_dev(col, torch.int32, dev)
+            if not (self.data.numel() == self.row.numel() == self.col.numel()):
+                raise ValueError("row, column, and data array must all be the same length")
+            if shape is None:
+                if self.row.numel() == 0:
+                    raise ValueError("cannot infer dimensions from zero sized index arrays")
+                shape = (int(self.row.max().item()) + 1, int(self.col.max().item()) + 1)
+            self._shape = (int(shape[0]), int(shape[1]))
+        else:
+            raise ValueError("Unsupported initializer format")
+
+    def tocsr(self, copy=False):
+        m, n = self.shape
+        nnz = self.nnz
+        cp = torch.empty(m + 1, dtype=torch.int32, device=self.device)
+        cj = torch.empty(nnz, dtype=torch.int32, device=self.device)
+        cx = torch.empty(nnz, dtype=self.data.dtype, device=self.device)
+        out = ctypes.c_int64(0)
+        h = self._handle()
+        _lib.check(h, _lib.load().b200sp_coo_to_csr(
+            h, _rtype(self.dtype), m, n, nnz, self.row.data_ptr(), self.col.data_ptr(), self.data.data_ptr(),
+            cp.data_ptr(), cj.data_ptr(), cx.data_ptr(), ctypes.byref(out)))
+        k = out.value
+        res = csr_matrix((cx if k == nnz else cx[:k].clone(), cj if k == nnz else cj[:k].clone(), cp), shape=(m, n))
+        res._canonical = True
+        return res
+
+    def tocsc(self, copy=False):
+        return self.tocsr().tocsc()
+
+    def tocoo(self, copy=False):
+        return self
+
+    def sum_duplicates(self):
+        """In place: sorted by (row, col), duplicates summed (_coo.py:356-459)."""
+        c = self.tocsr().tocoo()
+        self.row, self.col, self.data = c.row, c.col, c.data
+
+    def transpose(self, axes=None, copy=False):
+        return coo_matrix((self.data, (self.col, self.row)), shape=(self.shape[1], self.shape[0]))
+
+    @property
+    def T(self):
+        return self.transpose()
+
+
+class csc_matrix(_via_csr):
+    """Device CSC container (mirror of cupyx.scipy.sparse.csc_matrix, _csc.py): `.data/.indices`
+    (row indices) `/.indptr` (column pointers); `tocsr()` re-orders on the device
+    (_csc.py:304-326, cusparse.csc2csr)."""
+    format = "csc"
+
+    def __init__(self, arg1, shape=None, dtype=None, copy=False):
+        dev = _device()
+        if hasattr(arg1, "tocsc") and hasattr(arg1, "nnz") and not isinstance(arg1, (csr_matrix, _via_csr)):
+            c = arg1.tocsc()
+            dt = _check_dtype(dtype or c.dtype)
+            self.data = _to_dev(c.data.astype(dt, copy=False), _TORCH_DT[dt], dev)
+            self.indices = _to_dev(c.indices.astype(np.int32, copy=False), torch.int32, dev)
+            self.indptr = _to_dev(c.indptr.astype(np.int32, copy=False), torch.int32, dev)
+            self._shape = tuple(int(v) for v in c.shape)
+        elif isinstance(arg1, tuple) and len(arg1) == 3:
+            data, indices, indptr = arg1
+            if isinstance(data, torch.Tensor):
+                dt = _check_dtype(dtype or _NP_DT.get(data.dtype, None) or np.float32)
+            else:
+                dt = _check_dtype(dtype or np.asarray(data).dtype)
+            self.data = _to_dev(data, _TORCH_DT[dt], dev)
+            self.indices = _to_dev(indices, torch.int32, dev)
+            self.indptr = _to_dev(indptr, torch.int32, dev)
+            if shape is None:
+                nrows = int(self.indices.max().item()) + 1 if self.indices.numel() else 0
+                shape = (nrows, self.indptr.numel() - 1)
+            self._shape = (int(shape[0]), int(shape[1]))
+            if self.indptr.numel() != self._shape[1] + 1:
+                raise ValueError("index pointer size ({}) should be ({})".format(self.indptr.numel(), self._shape[1] + 1))
+            if self.data.numel() != self.indices.numel():
+                raise ValueError("indices and data should have the same size")
+        else:
+            raise ValueError("Unsupported initializer format")
+
+    def tocsr(self, copy=False):
+        m, n = self.shape
+        cp = torch.empty(m + 1, dtype=torch.int32, device=self.device)
+        cj = torch.empty(self.nnz, dtype=torch.int32, device=self.device)
+        cx = torch.empty(self.nnz, dtype=self.data.dtype, device=self.device)
+        h = self._handle()
+        _lib.check(h, _lib.load().b200sp_csc_to_csr(
+            h, _rtype(self.dtype), m, n, self.nnz, self.indptr.data_ptr(), self.indices.data_ptr(),
+            self.data.data_ptr(), cp.data_ptr(), cj.data_ptr(), cx.data_ptr()))
+        return csr_matrix((cx, cj, cp), shape=(m, n))
+
+    def tocsc(self, copy=False):
+        return self
+
+    def tocoo(self, copy=False):
+        return self.tocsr().tocoo()
+
+    def transpose(self, axes=None, copy=False):
+        """_csc.py:337-365: the same arrays read as the CSR of the transpose."""
+        return csr_matrix((self.data, self.indices, self.indptr), shape=(self.shape[1], self.shape[0]))
+
+    @property
+    def T(self):
+        return self.transpose()
+
+
+def max_abs_diff(a, b):
+    """max |a - b| of two CSR matrices of the same shape without forming dense arrays: the fused
+    form of `abs(C.toarray() - D.toarray()).max()` (numerical_error/error.py:25-29)."""
+    if not (isinstance(a, csr_matrix) and isinstance(b, csr_matrix)):
+        raise TypeError("max_abs_diff expects two csr_matrix operands")
+    if a.shape != b.shape:
+        raise ValueError("mismatched shape")
+    if a.dtype != b.dtype:
+        raise TypeError("mismatched dtype")
+    a.sum_duplicates()
+    b.sum_duplicates()
+    res = ctypes.c_double(0.0)
+    h = a._handle()
+    _lib.check(h, _lib.load().b200sp_csr_max_abs_diff(
+        h, _rtype(a.dtype), a.shape[0], a.indptr.data_ptr(), a.indices.data_ptr(), a.data.data_ptr(),
+        b.indptr.data_ptr(), b.indices.data_ptr(), b.data.data_ptr(), ctypes.byref(res)))
+    return res.value
+
+
 def isspmatrix_csr(x):
     return isinstance(x, csr_matrix)
+
+
+def isspmatrix(x):
+    return isinstance(x, (csr_matrix, csc_matrix, coo_matrix))

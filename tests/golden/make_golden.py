@@ -15,6 +15,8 @@ the reference's own input recipes:
 Outputs
   spgemm_small.npz   full A, B, C arrays of a few small cases (fp32 + fp64, rectangular, alpha)
   spmv_small.npz     A, x, y for SpMV cases
+  convert_small.npz  COO -> canonical CSR (duplicates at most two-fold, so SciPy's bits are
+                     well defined) and CSC -> CSR cases (scipy tocsr / sum_duplicates)
   checksums.json     sha256 of (indptr, indices, data bytes) of C for the whole 24-case grid, C1
                      and the light end of the C3 sweep - cases too big to commit as arrays
 
@@ -91,6 +93,23 @@ def main():
         mv[f"{name}/y"] = A @ x
         mv[f"{name}/shape"] = np.array(A.shape, dtype=np.int64)
     np.savez_compressed(os.path.join(HERE, "spmv_small.npz"), **mv)
+
+    cv = {}
+    for name, (m, n, k, seed, dt) in {"coo_pairs_40x30_f32": (40, 30, 300, 3, np.float32),
+                                      "coo_pairs_1x64_f64": (1, 64, 40, 4, np.float64),
+                                      "coo_pairs_257x3_f32": (257, 3, 500, 5, np.float32)}.items():
+        row, col, val = helpers.coo_with_pairs(m, n, k, seed, dt)
+        M = helpers.scipy_canonical_from_coo(row, col, val, (m, n))
+        cv[f"{name}/row"], cv[f"{name}/col"], cv[f"{name}/val"] = row, col, val
+        cv[f"{name}/Cp"], cv[f"{name}/Cj"], cv[f"{name}/Cx"] = M.indptr.astype(np.int32), M.indices.astype(np.int32), M.data
+        cv[f"{name}/shape"] = np.array([m, n], dtype=np.int64)
+    for name, (m, n, d, dt) in {"csc_50x70_f32": (50, 70, 0.2, np.float32), "csc_9x300_f64": (9, 300, 0.1, np.float64)}.items():
+        M = sp.random(m, n, density=d, format="csc", dtype=dt, random_state=np.random.RandomState(8))
+        R = M.tocsr()
+        cv[f"{name}/ptr"], cv[f"{name}/idx"], cv[f"{name}/val"] = M.indptr.astype(np.int32), M.indices.astype(np.int32), M.data
+        cv[f"{name}/Cp"], cv[f"{name}/Cj"], cv[f"{name}/Cx"] = R.indptr.astype(np.int32), R.indices.astype(np.int32), R.data
+        cv[f"{name}/shape"] = np.array([m, n], dtype=np.int64)
+    np.savez_compressed(os.path.join(HERE, "convert_small.npz"), **cv)
 
     sums = {"_scipy": scipy.__version__, "_numpy": np.__version__, "cases": {}}
     for n in helpers.GRID_SIZES:

@@ -78,3 +78,34 @@ def skewed_pair(seed=7, k=5000, n=300000, dtype=np.float32):
     A.sort_indices()
     B.sort_indices()
     return A, B
+
+
+def coo_with_pairs(m, n, k, seed, dtype=np.float32, dup_fraction=0.3):
+    """Unsorted COO triple in which every position occurs at most twice, so that the sum of
+    duplicates does not depend on their order (fp addition commutes) and SciPy's unstable
+    in-row sort cannot change the bits."""
+    rng = np.random.default_rng(seed)
+    k = min(k, m * n)
+    lin = rng.choice(m * n, size=k, replace=False)
+    dup = lin[rng.random(k) < dup_fraction]
+    lin = np.concatenate([lin, dup])
+    rng.shuffle(lin)
+    row, col = (lin // n).astype(np.int32), (lin % n).astype(np.int32)
+    return row, col, rng.standard_normal(lin.size).astype(dtype)
+
+
+def coo_heavy_duplicates(m, n, k, seed, dtype=np.float32):
+    """COO with many-fold duplicates (k draws with replacement, a few hot positions)."""
+    rng = np.random.default_rng(seed)
+    row = rng.integers(0, m, k).astype(np.int32)
+    col = rng.integers(0, n, k).astype(np.int32)
+    hot = rng.random(k) < 0.05
+    row[hot], col[hot] = m // 2, n // 3
+    return row, col, rng.standard_normal(k).astype(dtype)
+
+
+def scipy_canonical_from_coo(row, col, val, shape):
+    M = sp.coo_matrix((val, (row, col)), shape=shape).tocsr()
+    M.sum_duplicates()
+    M.sort_indices()
+    return M
