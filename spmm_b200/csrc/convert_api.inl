@@ -63,7 +63,7 @@ int radix_sort(b200sp_context *h, SortScratch &s, long long n, int lo_bits, int 
   int shifts[8], np = 0;
   for (int b = 0; b < lo_bits; b += 8) shifts[np++] = b;
   for (int b = 0; b < hi_bits; b += 8) shifts[np++] = 32 + b;
-  if (np == 0) shifts[np++] = 0;  // one pass anyway: it materialises the identity payload
+  if (np == 0) shifts[np++] = 32 + hi_bits;  // one pass on an all-zero digit: it materialises the identity payload
   int cur = 0;
   for (int p = 0; p < np; ++p) {
     k_rs_count<<<s.ntiles, RS_THREADS, 0, h->stream>>>(s.keys[cur], n, shifts[p], s.ntiles, s.counts);
