@@ -83,6 +83,8 @@ struct b200sp_context {
   int64_t bytes_live = 0, bytes_peak = 0;
   int64_t launches = 0;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaStream_t copy_stream = nullptr;  // second DMA queue of the *_host entry points (ingest pipeline)
+  cudaEvent_t ev_copy = nullptr, ev_sym = nullptr;
   float ms_symbolic = 0.f, ms_numeric = 0.f;
   bool numeric_timed = false;
   Plan plan;
@@ -221,6 +223,9 @@ extern "C" int b200sp_create(b200sp_handle_t *handle, int device) {
     return B200SP_ERR_CUDA;
   }
   for (auto &e : h->ev) cudaEventCreate(&e);
+  cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
+  cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&h->ev_sym, cudaEventDisableTiming);
   *handle = h;
   return B200SP_OK;
 }
@@ -245,6 +250,9 @@ extern "C" int b200sp_destroy(b200sp_handle_t h) {
   if (h->h_counters) cudaFreeHost(h->h_counters);
   for (auto &e : h->ev)
     if (e) cudaEventDestroy(e);
+  if (h->ev_copy) cudaEventDestroy(h->ev_copy);
+  if (h->ev_sym) cudaEventDestroy(h->ev_sym);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   delete h;
   return B200SP_OK;
 }
@@ -796,11 +804,13 @@ int ensure_pinned(b200sp_context *h, int i, size_t bytes) {
   return B200SP_OK;
 }
 
-int upload(b200sp_context *h, Buffer &b, const void *src, size_t bytes) {
+int upload_on(b200sp_context *h, cudaStream_t st, Buffer &b, const void *src, size_t bytes) {
   TRY(ensure(h, b, std::max<size_t>(bytes, 16)));
-  if (bytes) CUDA_TRY(h, cudaMemcpyAsync(b.ptr, src, bytes, cudaMemcpyHostToDevice, h->stream));
+  if (bytes) CUDA_TRY(h, cudaMemcpyAsync(b.ptr, src, bytes, cudaMemcpyHostToDevice, st));
   return B200SP_OK;
 }
+
+int upload(b200sp_context *h, Buffer &b, const void *src, size_t bytes) { return upload_on(h, h->stream, b, src, bytes); }
 
 }  // namespace
 
@@ -819,31 +829,55 @@ extern "C" int b200sp_spgemm_host(b200sp_handle_t h, int dtype, int64_t m, int64
     return fail(h, B200SP_ERR_INVALID, "bad CSR arrays");
   DeviceGuard guard(h->device);
   const bool alias = (hAp == hBp && hAj == hBj && hAx == hBx && m == k);
+  // Ingest pipeline (the reference times H2D inside the op:
+  // SpGEMM_alg_comparison/profiler.py:210-213).  The symbolic pass needs only the structure
+  // arrays, so those go first on the compute stream while the value arrays travel on a second
+  // DMA queue underneath the symbolic kernels; the numeric pass waits for them with an event.
+  // C.indptr is final after the symbolic pass and goes back under the numeric kernels.
+  cudaStream_t cs = h->copy_stream ? h->copy_stream : h->stream;
   TRY(upload(h, h->io[0], hAp, (size_t)(m + 1) * 4));
   TRY(upload(h, h->io[1], hAj, (size_t)nnzA * 4));
-  TRY(upload(h, h->io[2], hAx, (size_t)nnzA * vs));
   if (!alias) {
     TRY(upload(h, h->io[3], hBp, (size_t)(k + 1) * 4));
     TRY(upload(h, h->io[4], hBj, (size_t)nnzB * 4));
-    TRY(upload(h, h->io[5], hBx, (size_t)nnzB * vs));
   }
+  TRY(upload_on(h, cs, h->io[2], hAx, (size_t)nnzA * vs));
+  if (!alias) TRY(upload_on(h, cs, h->io[5], hBx, (size_t)nnzB * vs));
+  CUDA_TRY(h, cudaEventRecord(h->ev_copy, cs));
   const int bi = alias ? 0 : 3;
   TRY(ensure(h, h->io[6], (size_t)(m + 1) * 4));
   int64_t nc = 0;
-  TRY(b200sp_spgemm_symbolic(h, m, k, n, nnzA, nnzB, (const int *)h->io[0].ptr, (const int *)h->io[1].ptr,
-                             (const int *)h->io[bi].ptr, (const int *)h->io[bi + 1].ptr, alg, chunk_fraction,
-                             num_products, &nc, (int *)h->io[6].ptr));
-  TRY(ensure(h, h->io[7], std::max<size_t>((size_t)nc * 4, 16)));
-  TRY(ensure(h, h->io[8], std::max<size_t>((size_t)nc * vs, 16)));
-  TRY(b200sp_spgemm_numeric(h, dtype, alpha, h->io[2].ptr, h->io[bi + 2].ptr, (int *)h->io[7].ptr, h->io[8].ptr));
-  TRY(ensure_pinned(h, 0, (size_t)(m + 1) * 4));
-  TRY(ensure_pinned(h, 1, (size_t)nc * 4));
-  TRY(ensure_pinned(h, 2, (size_t)nc * vs));
-  CUDA_TRY(h, cudaMemcpyAsync(h->pinned_out[0], h->io[6].ptr, (size_t)(m + 1) * 4, cudaMemcpyDeviceToHost, h->stream));
+  int rc = b200sp_spgemm_symbolic(h, m, k, n, nnzA, nnzB, (const int *)h->io[0].ptr, (const int *)h->io[1].ptr,
+                                  (const int *)h->io[bi].ptr, (const int *)h->io[bi + 1].ptr, alg, chunk_fraction,
+                                  num_products, &nc, (int *)h->io[6].ptr);
+  if (rc != B200SP_OK) {
+    cudaStreamSynchronize(cs);  // the caller may free its value arrays as soon as we return
+    return rc;
+  }
+  rc = ensure_pinned(h, 0, (size_t)(m + 1) * 4);
+  if (rc == B200SP_OK) rc = ensure_pinned(h, 1, (size_t)nc * 4);
+  if (rc == B200SP_OK) rc = ensure_pinned(h, 2, (size_t)nc * vs);
+  if (rc == B200SP_OK) rc = ensure(h, h->io[7], std::max<size_t>((size_t)nc * 4, 16));
+  if (rc == B200SP_OK) rc = ensure(h, h->io[8], std::max<size_t>((size_t)nc * vs, 16));
+  if (rc != B200SP_OK) {
+    cudaStreamSynchronize(cs);
+    return rc;
+  }
+  // C.indptr is final once the symbolic pass is done
+  CUDA_TRY(h, cudaEventRecord(h->ev_sym, h->stream));
+  CUDA_TRY(h, cudaStreamWaitEvent(cs, h->ev_sym, 0));
+  CUDA_TRY(h, cudaMemcpyAsync(h->pinned_out[0], h->io[6].ptr, (size_t)(m + 1) * 4, cudaMemcpyDeviceToHost, cs));
+  CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->ev_copy, 0));
+  rc = b200sp_spgemm_numeric(h, dtype, alpha, h->io[2].ptr, h->io[bi + 2].ptr, (int *)h->io[7].ptr, h->io[8].ptr);
+  if (rc != B200SP_OK) {
+    cudaStreamSynchronize(cs);
+    return rc;
+  }
   if (nc) {
     CUDA_TRY(h, cudaMemcpyAsync(h->pinned_out[1], h->io[7].ptr, (size_t)nc * 4, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(h, cudaMemcpyAsync(h->pinned_out[2], h->io[8].ptr, (size_t)nc * vs, cudaMemcpyDeviceToHost, h->stream));
   }
+  CUDA_TRY(h, cudaStreamSynchronize(cs));
   CUDA_TRY(h, cudaStreamSynchronize(h->stream));
   *hCp = (int32_t *)h->pinned_out[0];
   *hCj = (int32_t *)h->pinned_out[1];
