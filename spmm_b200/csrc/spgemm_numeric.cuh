@@ -390,19 +390,194 @@ template <> struct Untouched<double> {
   static __device__ __forceinline__ bool is(double v) { return __double_as_longlong(v) == (long long)0xFFF8DEADBEEF0001LL; }
 };
 
-constexpr int DENSE_MAX_NT = 256;
-constexpr int DENSE_PAD = 8;  // zero-length staging entries after the chunk (prefetch runs ahead)
+constexpr int DENSE_MAX_NT = 192;  // 3 CTAs of 6 warps: at most 5 warps per scheduler partition, 96 registers each
+constexpr int DENSE_DEPTH = 8;      // B-row pieces whose loads are in flight ahead of the one being applied
+constexpr int DENSE_PAD = 2 * DENSE_DEPTH;  // zero-length staging entries after the last piece: the prefetch reads up to cnt + 2 D - 1
+constexpr int DENSE_CAP = 2 * DENSE_MAX_NT;  // staged pieces per round
+
+// One staged piece of a B row (at most blockDim.x entries): where it starts, how long it is, and
+// the A value it is scaled by (read back with one LDS.128).
+template <typename T> struct __align__(16) DenseSeg {
+  int start, len;
+  T a;
+};
+
+// The pieces staged in s_seg[0 .. cnt) applied to the accumulator in order, one barrier per
+// piece.  Software pipeline: the (column, value) loads of pieces q+1 .. q+D are in flight while
+// piece q is applied (the L2 round trip is ~5 barrier steps long), and the staging entry of the
+// next fetch is read one step early, so nothing but the accumulator read itself waits on shared
+// memory.  The thread's index into a piece is clamped to the last entry of B, not to the piece:
+// lanes past its end load a neighbour's entry and discard it.
+template <typename T, int D>
+__device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const DenseSeg<T> *s_seg, int cnt, int tid,
+                                                   const int *__restrict__ Bj, const T *__restrict__ Bx, int last) {
+  int j[D], len[D];
+  T b[D], a[D];
+  DenseSeg<T> nx = s_seg[0];
+#define DENSE_FETCH(S, Q)                       \
+  {                                             \
+    len[S] = nx.len;                            \
+    a[S] = nx.a;                                \
+    const int idx_ = min(nx.start + tid, last); \
+    nx = s_seg[(Q) + 1];                        \
+    j[S] = __ldg(Bj + idx_);                    \
+    b[S] = __ldg(Bx + idx_);                    \
+  }
+#pragma unroll
+  for (int s = 0; s < D; ++s) DENSE_FETCH(s, s)
+  for (int q = 0; q < cnt; q += D) {
+#pragma unroll
+    for (int s = 0; s < D; ++s) {
+      if (len[s]) {  // CTA-uniform; only the padding after the last piece is empty
+        if (tid < len[s]) {
+          const T cur = acc[j[s]];
+          acc[j[s]] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, mul_rn(a[s], b[s]));
+        }
+        __syncthreads();
+      }
+      DENSE_FETCH(s, q + D + s)
+    }
+  }
+#undef DENSE_FETCH
+}
+
+// Output sweep of one warp's column range [c_lo, c_hi) (multiples of 128; the accumulator is
+// padded with untouched columns): ordered emit with ballot + popc, accumulator reset on the way.
+template <typename T, bool SCALE>
+__device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ cj,
+                                           T *__restrict__ cx, int pos, T alpha) {
+  const T UNT = Untouched<T>::value();
+  const unsigned below = (1u << lane) - 1u;
+#pragma unroll 4
+  for (int c = c_lo + lane; c < c_hi; c += 32) {
+    const T v = acc[c];
+    const bool touched = !Untouched<T>::is(v);
+    const unsigned bal = __ballot_sync(FULL, touched);
+    if (touched) {
+      const int o = pos + __popc(bal & below);
+      cj[o] = c;
+      cx[o] = SCALE ? mul_rn(alpha, v) : v;
+      acc[c] = UNT;
+    }
+    pos += __popc(bal);
+  }
+}
+
+template <typename T> struct Vec4;
+template <> struct Vec4<float> {
+  static __device__ __forceinline__ int touched(const float *p) {
+    const float4 v = *reinterpret_cast<const float4 *>(p);
+    return !Untouched<float>::is(v.x) + !Untouched<float>::is(v.y) + !Untouched<float>::is(v.z) + !Untouched<float>::is(v.w);
+  }
+};
+template <> struct Vec4<double> {
+  static __device__ __forceinline__ int touched(const double *p) {
+    const double2 u = *reinterpret_cast<const double2 *>(p), v = *reinterpret_cast<const double2 *>(p + 2);
+    return !Untouched<double>::is(u.x) + !Untouched<double>::is(u.y) + !Untouched<double>::is(v.x) + !Untouched<double>::is(v.y);
+  }
+};
 
 template <typename T>
-__global__ void __launch_bounds__(DENSE_MAX_NT, 1)
+__global__ void __launch_bounds__(DENSE_MAX_NT, 3)
 k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
+                const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
+                const int *__restrict__ Bj, const T *__restrict__ Bx, int nnzB, const int *__restrict__ Cp,
+                int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];  // round_up(n, 128) accumulator columns
+  __shared__ DenseSeg<T> s_seg[DENSE_CAP + DENSE_PAD];       // the staged pieces of the round
+  __shared__ int s_wcnt[DENSE_MAX_NT / 32];
+  __shared__ int s_scan[DENSE_MAX_NT / 32];
+  T *acc = reinterpret_cast<T *>(smem_raw);
+  const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
+  const T UNT = Untouched<T>::value();
+  const int npad = (n + 127) & ~127;
+  for (int c = tid; c < npad; c += NT) acc[c] = UNT;
+  // columns per warp for the output sweep, a multiple of 128
+  const int cpw = ((npad + nw - 1) / nw + 127) & ~127;
+  const int c_lo = min(w * cpw, npad), c_hi = min(c_lo + cpw, npad);
+  __syncthreads();
+
+  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
+    const int row = rows[ridx];
+    const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
+    for (int base = a_begin; base < a_end; base += NT) {
+      // ---- stage: thread t takes A nonzero base+t; its B row is cut into pieces of <= NT
+      //      entries; an exclusive scan of the piece counts gives every piece its slot, in A order
+      const int t = base + tid;
+      int start = 0, len = 0;
+      T av = T(0);
+      if (t < a_end) {
+        const int kk = __ldg(Aj + t);
+        start = __ldg(Bp + kk);
+        len = __ldg(Bp + kk + 1) - start;
+        av = __ldg(Ax + t);
+      }
+      const int pieces = (len + NT - 1) / NT;  // 0 for an empty B row: it gets no slot at all
+      int inc = pieces;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(FULL, inc, o);
+        if (lane >= o) inc += u;
+      }
+      if (lane == 31) s_scan[w] = inc;
+      __syncthreads();
+      int off = inc - pieces, total = 0;
+      for (int q = 0; q < nw; ++q) {
+        const int v = s_scan[q];
+        if (q < w) off += v;
+        total += v;
+      }
+      for (int r0 = 0; r0 < total; r0 += DENSE_CAP) {
+        const int cnt = min(DENSE_CAP, total - r0);
+        const int p_lo = max(0, r0 - off), p_hi = min(pieces, r0 + DENSE_CAP - off);
+        for (int pc = p_lo; pc < p_hi; ++pc) {
+          DenseSeg<T> sg;
+          sg.start = start + pc * NT;
+          sg.len = min(NT, len - pc * NT);
+          sg.a = av;
+          s_seg[off + pc - r0] = sg;
+        }
+        if (tid < DENSE_PAD) {
+          DenseSeg<T> z;
+          z.start = 0;
+          z.len = 0;
+          z.a = T(0);
+          s_seg[cnt + tid] = z;
+        }
+        __syncthreads();
+        dense_apply_staged<T, DENSE_DEPTH>(acc, s_seg, cnt, tid, Bj, Bx, nnzB - 1);
+        __syncthreads();
+      }
+      if (total == 0) __syncthreads();  // s_scan is rewritten by the next chunk
+    }
+    // ---- output: warp w owns columns [c_lo, c_hi); count, prefix over the warps, ordered emit ----
+    int mine = 0;
+    for (int c = c_lo + 4 * lane; c < c_hi; c += 128) mine += Vec4<T>::touched(acc + c);
+    mine = warp_sum(mine);
+    if (lane == 0) s_wcnt[w] = mine;
+    __syncthreads();
+    int pos = 0;
+    for (int q = 0; q < w; ++q) pos += s_wcnt[q];
+    const int out0 = __ldg(Cp + row);
+    if (alpha == T(1)) dense_emit<T, false>(acc, c_lo, c_hi, lane, Cj + out0, Cx + out0, pos, alpha);
+    else dense_emit<T, true>(acc, c_lo, c_hi, lane, Cj + out0, Cx + out0, pos, alpha);
+    __syncthreads();
+  }
+}
+
+// TEMPORARY A/B copy of the previous dense kernel (experiment only)
+constexpr int OLD_MAX_NT = 256;
+constexpr int OLD_PAD = 8;
+template <typename T>
+__global__ void __launch_bounds__(OLD_MAX_NT, 1)
+k_num_dense_cta_old(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
                 const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
                 const int *__restrict__ Bj, const T *__restrict__ Bx, const int *__restrict__ Cp,
                 int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ int2 s_seg[DENSE_MAX_NT + DENSE_PAD];  // {start, len} of the staged B rows
-  __shared__ T s_a[DENSE_MAX_NT + DENSE_PAD];       // their A values
-  __shared__ int s_wcnt[DENSE_MAX_NT / 32];
+  __shared__ int2 s_seg[OLD_MAX_NT + OLD_PAD];  // {start, len} of the staged B rows
+  __shared__ T s_a[OLD_MAX_NT + OLD_PAD];       // their A values
+  __shared__ int s_wcnt[OLD_MAX_NT / 32];
   T *acc = reinterpret_cast<T *>(smem_raw);
   const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
   const T UNT = Untouched<T>::value();
@@ -412,7 +587,7 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
   __syncthreads();
 
 // One B row: this thread's entry (index clamped, so the loads need no branch) ...
-#define DENSE_FETCH(J, B, SG, Q)                                  \
+#define OLD_FETCH(J, B, SG, Q)                                  \
   {                                                               \
     SG = s_seg[Q];                                                \
     const int idx_ = SG.x + min(tid, max(SG.y - 1, 0));           \
@@ -420,7 +595,7 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
     B = __ldg(Bx + idx_);                                         \
   }
 // ... applied in A-row order, one barrier per non-empty B row.
-#define DENSE_APPLY(J, B, SG, Q)                                                         \
+#define OLD_APPLY(J, B, SG, Q)                                                         \
   if (SG.y) { /* CTA-uniform */                                                          \
     const T a_ = s_a[Q];                                                                 \
     if (tid < SG.y) {                                                                    \
@@ -453,7 +628,7 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
       }
       s_seg[tid] = sg;
       s_a[tid] = av;
-      if (tid < DENSE_PAD) s_seg[NT + tid] = make_int2(0, 0);
+      if (tid < OLD_PAD) s_seg[NT + tid] = make_int2(0, 0);
       __syncthreads();
       const int cnt = min(NT, a_end - base);  // entries [cnt, NT + PAD) have length 0
       // rolling 4-deep register prefetch: the loads of B rows q+4.. are in flight while row q
@@ -461,24 +636,24 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
       int2 g0, g1, g2, g3;
       int j0, j1, j2, j3;
       T b0, b1, b2, b3;
-      DENSE_FETCH(j0, b0, g0, 0)
-      DENSE_FETCH(j1, b1, g1, 1)
-      DENSE_FETCH(j2, b2, g2, 2)
-      DENSE_FETCH(j3, b3, g3, 3)
+      OLD_FETCH(j0, b0, g0, 0)
+      OLD_FETCH(j1, b1, g1, 1)
+      OLD_FETCH(j2, b2, g2, 2)
+      OLD_FETCH(j3, b3, g3, 3)
       for (int q = 0; q < cnt; q += 4) {
-        DENSE_APPLY(j0, b0, g0, q)
-        DENSE_FETCH(j0, b0, g0, q + 4)
-        DENSE_APPLY(j1, b1, g1, q + 1)
-        DENSE_FETCH(j1, b1, g1, q + 5)
-        DENSE_APPLY(j2, b2, g2, q + 2)
-        DENSE_FETCH(j2, b2, g2, q + 6)
-        DENSE_APPLY(j3, b3, g3, q + 3)
-        DENSE_FETCH(j3, b3, g3, q + 7)
+        OLD_APPLY(j0, b0, g0, q)
+        OLD_FETCH(j0, b0, g0, q + 4)
+        OLD_APPLY(j1, b1, g1, q + 1)
+        OLD_FETCH(j1, b1, g1, q + 5)
+        OLD_APPLY(j2, b2, g2, q + 2)
+        OLD_FETCH(j2, b2, g2, q + 6)
+        OLD_APPLY(j3, b3, g3, q + 3)
+        OLD_FETCH(j3, b3, g3, q + 7)
       }
       __syncthreads();
     }
-#undef DENSE_FETCH
-#undef DENSE_APPLY
+#undef OLD_FETCH
+#undef OLD_APPLY
     // ---- output: warp w owns columns [w*cpw, (w+1)*cpw); count, prefix, then ordered emit ----
     const int c_lo = min(w * cpw, n), c_hi = min(c_lo + cpw, n);
     int mine = 0;
@@ -507,7 +682,6 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
   }
 }
 
-// ---- CTA per row, dense accumulator over one COLUMN BLOCK at a time --------------------------
 // For matrices too wide for k_num_dense_cta (n * sizeof(T) > shared memory) and rows of C with
 // many entries: the n columns are cut into nblk blocks of W columns; for each block the CTA
 // walks the A row once and applies only the part of every B row that falls into the block (B
