@@ -465,7 +465,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
         if (const char *e = getenv("B200SP_DENSE_NT")) nt = std::max(32, std::min(DENSE_MAX_NT, atoi(e) / 32 * 32));
         TRY(set_smem(h, k_num_dense_cta<T>, smem));
-        k_num_dense_cta<T><<<persistent_grid(cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha);
+        k_num_dense_cta<T><<<persistent_grid(cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, getenv("B200SP_DENSE_FLAGS") ? atoi(getenv("B200SP_DENSE_FLAGS")) : 0);
         return check_launch(h, "k_num_dense_cta");
       }
       // fp64 with n between the fp32 and fp64 budgets: column blocks

@@ -408,7 +408,7 @@ template <typename T> struct __align__(16) DenseSeg {
 // next fetch is read one step early, so nothing but the accumulator read itself waits on shared
 // memory.  The thread's index into a piece is clamped to the last entry of B, not to the piece:
 // lanes past its end load a neighbour's entry and discard it.
-template <typename T, int D>
+template <typename T, int D, bool REORDER>
 __device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const DenseSeg<T> *s_seg, int cnt, int tid,
                                                    const int *__restrict__ Bj, const T *__restrict__ Bx, int last) {
   int j[D], len[D];
@@ -428,24 +428,61 @@ __device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const De
   for (int q = 0; q < cnt; q += D) {
 #pragma unroll
     for (int s = 0; s < D; ++s) {
-      if (len[s]) {  // CTA-uniform; only the padding after the last piece is empty
-        if (tid < len[s]) {
-          const T cur = acc[j[s]];
-          acc[j[s]] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, mul_rn(a[s], b[s]));
-        }
-        __syncthreads();
-      }
-      DENSE_FETCH(s, q + D + s)
+      // the accumulator read goes first; the next fetch is issued underneath its latency
+      const bool piece = len[s] != 0;  // CTA-uniform; only the padding after the last piece is empty
+      const bool act = tid < len[s];
+      T *slot = acc + j[s];
+      T cur = T(0);
+      if (act) cur = *slot;
+      const T prod = mul_rn(a[s], b[s]);
+      if (REORDER) DENSE_FETCH(s, q + D + s)
+      if (act) *slot = add_rn(Untouched<T>::is(cur) ? T(0) : cur, prod);
+      if (piece) __syncthreads();
+      if (!REORDER) DENSE_FETCH(s, q + D + s)
     }
   }
 #undef DENSE_FETCH
 }
 
-// Output sweep of one warp's column range [c_lo, c_hi) (multiples of 128; the accumulator is
-// padded with untouched columns): ordered emit with ballot + popc, accumulator reset on the way.
+// Four consecutive accumulator columns per lane (one or two LDS.128).
+template <typename T> struct Vec4;
+template <> struct Vec4<float> {
+  static __device__ __forceinline__ void load(const float *p, float (&v)[4]) {
+    const float4 t = *reinterpret_cast<const float4 *>(p);
+    v[0] = t.x, v[1] = t.y, v[2] = t.z, v[3] = t.w;
+  }
+  static __device__ __forceinline__ void fill(float *p, float x) { *reinterpret_cast<float4 *>(p) = make_float4(x, x, x, x); }
+};
+template <> struct Vec4<double> {
+  static __device__ __forceinline__ void load(const double *p, double (&v)[4]) {
+    const double2 t = *reinterpret_cast<const double2 *>(p), u = *reinterpret_cast<const double2 *>(p + 2);
+    v[0] = t.x, v[1] = t.y, v[2] = u.x, v[3] = u.y;
+  }
+  static __device__ __forceinline__ void fill(double *p, double x) {
+    *reinterpret_cast<double2 *>(p) = make_double2(x, x);
+    *reinterpret_cast<double2 *>(p + 2) = make_double2(x, x);
+  }
+};
+
+// Touched columns of one warp's range [c_lo, c_hi) (multiples of 128; the accumulator is padded
+// with untouched columns).
+template <typename T>
+__device__ __forceinline__ int dense_count(const T *acc, int c_lo, int c_hi, int lane) {
+  int mine = 0;
+  for (int c = c_lo + 4 * lane; c < c_hi; c += 128) {
+    T v[4];
+    Vec4<T>::load(acc + c, v);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) mine += !Untouched<T>::is(v[e]);
+  }
+  return warp_sum(mine);
+}
+
+// Ordered emit of that range, 32 columns per step (fully coalesced stores: the better choice for
+// well-filled rows).
 template <typename T, bool SCALE>
-__device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ cj,
-                                           T *__restrict__ cx, int pos, T alpha) {
+__device__ __forceinline__ void dense_emit_ballot(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ Cj,
+                                                  T *__restrict__ Cx, int pos, T alpha) {
   const T UNT = Untouched<T>::value();
   const unsigned below = (1u << lane) - 1u;
 #pragma unroll 4
@@ -455,34 +492,58 @@ __device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane,
     const unsigned bal = __ballot_sync(FULL, touched);
     if (touched) {
       const int o = pos + __popc(bal & below);
-      cj[o] = c;
-      cx[o] = SCALE ? mul_rn(alpha, v) : v;
+      Cj[o] = c;
+      Cx[o] = SCALE ? mul_rn(alpha, v) : v;
       acc[c] = UNT;
     }
     pos += __popc(bal);
   }
 }
 
-template <typename T> struct Vec4;
-template <> struct Vec4<float> {
-  static __device__ __forceinline__ int touched(const float *p) {
-    const float4 v = *reinterpret_cast<const float4 *>(p);
-    return !Untouched<float>::is(v.x) + !Untouched<float>::is(v.y) + !Untouched<float>::is(v.z) + !Untouched<float>::is(v.w);
+// Ordered emit of that range, 128 columns per step: lane l owns columns c+4l .. c+4l+3, a warp
+// scan of the per-lane counts gives its output offset; the accumulator is reset on the way.
+template <typename T, bool SCALE>
+__device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ Cj,
+                                           T *__restrict__ Cx, int pos, T alpha) {
+  const T UNT = Untouched<T>::value();
+  for (int c = c_lo + 4 * lane; c < c_hi; c += 128) {
+    T v[4];
+    Vec4<T>::load(acc + c, v);
+    bool t[4];
+    int cnt = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      t[e] = !Untouched<T>::is(v[e]);
+      cnt += t[e];
+    }
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(FULL, inc, o);
+      if (lane >= o) inc += u;
+    }
+    int o = pos + inc - cnt;
+    if (cnt) {
+      Vec4<T>::fill(acc + c, UNT);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        if (t[e]) {
+          Cj[o] = c + e;
+          Cx[o] = SCALE ? mul_rn(alpha, v[e]) : v[e];
+          ++o;
+        }
+      }
+    }
+    pos += __shfl_sync(FULL, inc, 31);
   }
-};
-template <> struct Vec4<double> {
-  static __device__ __forceinline__ int touched(const double *p) {
-    const double2 u = *reinterpret_cast<const double2 *>(p), v = *reinterpret_cast<const double2 *>(p + 2);
-    return !Untouched<double>::is(u.x) + !Untouched<double>::is(u.y) + !Untouched<double>::is(v.x) + !Untouched<double>::is(v.y);
-  }
-};
+}
 
 template <typename T>
 __global__ void __launch_bounds__(DENSE_MAX_NT, 3)
 k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
                 const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
                 const int *__restrict__ Bj, const T *__restrict__ Bx, int nnzB, const int *__restrict__ Cp,
-                int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
+                int *__restrict__ Cj, T *__restrict__ Cx, T alpha, int flags) {
   extern __shared__ __align__(16) unsigned char smem_raw[];  // round_up(n, 128) accumulator columns
   __shared__ DenseSeg<T> s_seg[DENSE_CAP + DENSE_PAD];       // the staged pieces of the round
   __shared__ int s_wcnt[DENSE_MAX_NT / 32];
@@ -545,22 +606,28 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
           s_seg[cnt + tid] = z;
         }
         __syncthreads();
-        dense_apply_staged<T, DENSE_DEPTH>(acc, s_seg, cnt, tid, Bj, Bx, nnzB - 1);
+        if (flags & 2) dense_apply_staged<T, DENSE_DEPTH, false>(acc, s_seg, cnt, tid, Bj, Bx, nnzB - 1);
+        else dense_apply_staged<T, DENSE_DEPTH, true>(acc, s_seg, cnt, tid, Bj, Bx, nnzB - 1);
         __syncthreads();
       }
       if (total == 0) __syncthreads();  // s_scan is rewritten by the next chunk
     }
     // ---- output: warp w owns columns [c_lo, c_hi); count, prefix over the warps, ordered emit ----
-    int mine = 0;
-    for (int c = c_lo + 4 * lane; c < c_hi; c += 128) mine += Vec4<T>::touched(acc + c);
-    mine = warp_sum(mine);
+    const int mine = dense_count<T>(acc, c_lo, c_hi, lane);
     if (lane == 0) s_wcnt[w] = mine;
     __syncthreads();
-    int pos = 0;
+    int pos = __ldg(Cp + row);
     for (int q = 0; q < w; ++q) pos += s_wcnt[q];
-    const int out0 = __ldg(Cp + row);
-    if (alpha == T(1)) dense_emit<T, false>(acc, c_lo, c_hi, lane, Cj + out0, Cx + out0, pos, alpha);
-    else dense_emit<T, true>(acc, c_lo, c_hi, lane, Cj + out0, Cx + out0, pos, alpha);
+    // well-filled rows: 32 columns per step with fully coalesced stores; sparse rows: 128 columns
+    // per step (a quarter of the instructions, stores strided by the fill)
+    const int row_nnz = __ldg(Cp + row + 1) - __ldg(Cp + row);
+    if ((flags & 1) || (!(flags & 4) && row_nnz > (npad >> 2))) {
+      if (alpha == T(1)) dense_emit_ballot<T, false>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
+      else dense_emit_ballot<T, true>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
+    } else {
+      if (alpha == T(1)) dense_emit<T, false>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
+      else dense_emit<T, true>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
+    }
     __syncthreads();
   }
 }
