@@ -395,6 +395,25 @@ constexpr int DENSE_DEPTH = 8;      // B-row pieces whose loads are in flight ah
 constexpr int DENSE_PAD = 2 * DENSE_DEPTH;  // zero-length staging entries after the last piece: the prefetch reads up to cnt + 2 D - 1
 constexpr int DENSE_CAP = 2 * DENSE_MAX_NT;  // staged pieces per round
 
+// Global loads that stay where they are written: the compiler sinks read-only (ld.global.nc)
+// loads across bar.sync to shorten register lifetimes, which collapses a software pipeline that
+// is built around barriers; a volatile asm load keeps its place in the instruction stream.
+__device__ __forceinline__ int ld_inplace(const int *p) {
+  int v;
+  asm volatile("ld.global.s32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float ld_inplace(const float *p) {
+  float v;
+  asm volatile("ld.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ double ld_inplace(const double *p) {
+  double v;
+  asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+
 // One staged piece of a B row (at most blockDim.x entries): where it starts, how long it is, and
 // the A value it is scaled by (read back with one LDS.128).
 template <typename T> struct __align__(16) DenseSeg {
@@ -420,8 +439,8 @@ __device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const De
     a[S] = nx.a;                                \
     const int idx_ = min(nx.start + tid, last); \
     nx = s_seg[(Q) + 1];                        \
-    j[S] = __ldg(Bj + idx_);                    \
-    b[S] = __ldg(Bx + idx_);                    \
+    j[S] = ld_inplace(Bj + idx_);               \
+    b[S] = ld_inplace(Bx + idx_);               \
   }
 #pragma unroll
   for (int s = 0; s < D; ++s) DENSE_FETCH(s, s)
