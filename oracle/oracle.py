@@ -68,10 +68,25 @@ def row_products(Ap, Aj, Bp):
     return out
 
 
-def spgemm(A, B, n_cols, alpha=1.0, nthreads=1):
+def drop_zero_entries(C):
+    """SciPy's csr_matmat emits an entry only `if (sums[head] != 0)` (sparsetools csr.h, second
+    pass): results that are exactly +-0.0 - cancellation, products of explicit zeros - are not
+    stored, although csr_matmat_maxnnz counted them.  cuSPARSE (the path the product replaces)
+    keeps the structural pattern.  This filter turns the structural result into SciPy's."""
+    Cp, Cj, Cx = C
+    keep = Cx != 0
+    rows = np.repeat(np.arange(len(Cp) - 1), np.diff(Cp))
+    newp = np.zeros(len(Cp), dtype=Cp.dtype)
+    np.cumsum(np.bincount(rows[keep], minlength=len(Cp) - 1), out=newp[1:])
+    return newp, Cj[keep], Cx[keep]
+
+
+def spgemm(A, B, n_cols, alpha=1.0, nthreads=1, drop_zeros=False):
     """C = alpha * (A @ B).  A, B are (indptr, indices, data) triples; n_cols = B.shape[1].
 
     Returns (indptr, indices, data) with sorted rows, dtype of A's data (float32 / float64).
+    drop_zeros=False: structural pattern (cuSPARSE semantics, what the product implements);
+    drop_zeros=True: SciPy's output, which omits entries whose sum is exactly zero.
     """
     Ap, Aj, Ax = A
     Bp, Bj, Bx = B
@@ -100,7 +115,7 @@ def spgemm(A, B, n_cols, alpha=1.0, nthreads=1):
             _p(Cx, vp), ctypes.c_int(nthreads))
     if rc != 0:
         raise RuntimeError(f"oracle numeric failed ({rc})")
-    return Cp, Cj, Cx
+    return drop_zero_entries((Cp, Cj, Cx)) if drop_zeros else (Cp, Cj, Cx)
 
 
 def spmv(A, x, y=None, alpha=1.0, beta=0.0):

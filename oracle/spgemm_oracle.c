@@ -17,8 +17,12 @@
  * separately rounded products (no fused multiply-add; build with -ffp-contract=off).
  * SciPy emits each row's columns in reverse first-touch order; the reference generators call
  * sort_indices() before saving (cupy_cusparse/gen_and_save_alg1_txt.py:23-24) and cuSPARSE
- * returns sorted rows, so the oracle sorts each row's columns.  Entries that cancel to 0.0
- * stay stored (structural nnz), as in both SciPy and cuSPARSE.
+ * returns sorted rows, so the oracle sorts each row's columns.  Entries whose sum is exactly 0.0
+ * (cancellation, products of explicit zeros) stay stored: that is the structural pattern
+ * cuSPARSE returns (the path the product replaces; checked on the GPU against the reference's own
+ * drivers, tests/test_gpu_vs_reference.py).  SciPy's csr_matmat drops them in its second pass
+ * (`if (sums[head] != 0)`); oracle.py: spgemm(..., drop_zeros=True) applies that filter, and the
+ * tests pin both forms.
  *
  * Pinning.  tests/test_oracle.py checks this file against (a) the literal 3x4 / 4x3 fixtures of
  * modify_src/cupy-src/tests/cupyx_tests/scipy_tests/sparse_tests/test_csr.py:25-135 with

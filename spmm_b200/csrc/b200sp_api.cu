@@ -456,12 +456,6 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       if ((size_t)p.n * sizeof(T) <= SMEM_DENSE_MAX) {
         const size_t smem = (((size_t)p.n + 127) & ~(size_t)127) * sizeof(T);  // padded to whole 128-column groups
         const double avgB = p.k ? (double)p.nnzB / (double)p.k : 0.0;
-        if (getenv("B200SP_DENSE_OLD")) {
-          const int nto = std::max(64, std::min(OLD_MAX_NT, (int)((avgB + 31) / 32) * 32));
-          TRY(set_smem(h, k_num_dense_cta_old<T>, smem));
-          k_num_dense_cta_old<T><<<persistent_grid(cnt, smem + 4352), nto, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
-          return check_launch(h, "k_num_dense_cta_old");
-        }
         int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
         if (const char *e = getenv("B200SP_DENSE_NT")) nt = std::max(32, std::min(DENSE_MAX_NT, atoi(e) / 32 * 32));
         TRY(set_smem(h, k_num_dense_cta<T>, smem));

@@ -390,6 +390,22 @@ template <> struct Untouched<double> {
   static __device__ __forceinline__ bool is(double v) { return __double_as_longlong(v) == (long long)0xFFF8DEADBEEF0001LL; }
 };
 
+// k_num_dense_cta marks an untouched column with -0.0 instead: every product is canonicalised
+// (p + 0.0 turns a -0.0 product into +0.0 and changes nothing else), so that
+//   (-0.0) + p' = (+0.0) + p   bit for bit,
+// the first add needs no special case, and an accumulator that has been touched can never be
+// -0.0 again (x + y = -0.0 only for x = y = -0.0).  The read-modify-write chain is then
+// LDS -> FADD -> STS with no compare / select in it.
+template <typename T> struct NegZero;
+template <> struct NegZero<float> {
+  static __device__ __forceinline__ float value() { return __int_as_float((int)0x80000000); }
+  static __device__ __forceinline__ bool is(float v) { return __float_as_int(v) == (int)0x80000000; }
+};
+template <> struct NegZero<double> {
+  static __device__ __forceinline__ double value() { return __longlong_as_double((long long)0x8000000000000000ULL); }
+  static __device__ __forceinline__ bool is(double v) { return __double_as_longlong(v) == (long long)0x8000000000000000ULL; }
+};
+
 constexpr int DENSE_MAX_NT = 192;  // 3 CTAs of 6 warps: at most 5 warps per scheduler partition, 96 registers each
 constexpr int DENSE_DEPTH = 8;      // B-row pieces whose loads are in flight ahead of the one being applied
 constexpr int DENSE_PAD = 2 * DENSE_DEPTH;  // zero-length staging entries after the last piece: the prefetch reads up to cnt + 2 D - 1
@@ -453,9 +469,9 @@ __device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const De
       T *slot = acc + j[s];
       T cur = T(0);
       if (act) cur = *slot;
-      const T prod = mul_rn(a[s], b[s]);
+      const T prod = add_rn(mul_rn(a[s], b[s]), T(0));  // -0.0 -> +0.0
       if (REORDER) DENSE_FETCH(s, q + D + s)
-      if (act) *slot = add_rn(Untouched<T>::is(cur) ? T(0) : cur, prod);
+      if (act) *slot = add_rn(cur, prod);
       if (piece) __syncthreads();
       if (!REORDER) DENSE_FETCH(s, q + D + s)
     }
@@ -492,7 +508,7 @@ __device__ __forceinline__ int dense_count(const T *acc, int c_lo, int c_hi, int
     T v[4];
     Vec4<T>::load(acc + c, v);
 #pragma unroll
-    for (int e = 0; e < 4; ++e) mine += !Untouched<T>::is(v[e]);
+    for (int e = 0; e < 4; ++e) mine += !NegZero<T>::is(v[e]);
   }
   return warp_sum(mine);
 }
@@ -502,12 +518,12 @@ __device__ __forceinline__ int dense_count(const T *acc, int c_lo, int c_hi, int
 template <typename T, bool SCALE>
 __device__ __forceinline__ void dense_emit_ballot(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ Cj,
                                                   T *__restrict__ Cx, int pos, T alpha) {
-  const T UNT = Untouched<T>::value();
+  const T UNT = NegZero<T>::value();
   const unsigned below = (1u << lane) - 1u;
 #pragma unroll 4
   for (int c = c_lo + lane; c < c_hi; c += 32) {
     const T v = acc[c];
-    const bool touched = !Untouched<T>::is(v);
+    const bool touched = !NegZero<T>::is(v);
     const unsigned bal = __ballot_sync(FULL, touched);
     if (touched) {
       const int o = pos + __popc(bal & below);
@@ -524,7 +540,7 @@ __device__ __forceinline__ void dense_emit_ballot(T *acc, int c_lo, int c_hi, in
 template <typename T, bool SCALE>
 __device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ Cj,
                                            T *__restrict__ Cx, int pos, T alpha) {
-  const T UNT = Untouched<T>::value();
+  const T UNT = NegZero<T>::value();
   for (int c = c_lo + 4 * lane; c < c_hi; c += 128) {
     T v[4];
     Vec4<T>::load(acc + c, v);
@@ -532,7 +548,7 @@ __device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane,
     int cnt = 0;
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      t[e] = !Untouched<T>::is(v[e]);
+      t[e] = !NegZero<T>::is(v[e]);
       cnt += t[e];
     }
     int inc = cnt;
@@ -569,7 +585,7 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
   __shared__ int s_scan[DENSE_MAX_NT / 32];
   T *acc = reinterpret_cast<T *>(smem_raw);
   const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
-  const T UNT = Untouched<T>::value();
+  const T UNT = NegZero<T>::value();
   const int npad = (n + 127) & ~127;
   for (int c = tid; c < npad; c += NT) acc[c] = UNT;
   // columns per warp for the output sweep, a multiple of 128
@@ -646,123 +662,6 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
     } else {
       if (alpha == T(1)) dense_emit<T, false>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
       else dense_emit<T, true>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
-    }
-    __syncthreads();
-  }
-}
-
-// TEMPORARY A/B copy of the previous dense kernel (experiment only)
-constexpr int OLD_MAX_NT = 256;
-constexpr int OLD_PAD = 8;
-template <typename T>
-__global__ void __launch_bounds__(OLD_MAX_NT, 1)
-k_num_dense_cta_old(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
-                const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
-                const int *__restrict__ Bj, const T *__restrict__ Bx, const int *__restrict__ Cp,
-                int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ int2 s_seg[OLD_MAX_NT + OLD_PAD];  // {start, len} of the staged B rows
-  __shared__ T s_a[OLD_MAX_NT + OLD_PAD];       // their A values
-  __shared__ int s_wcnt[OLD_MAX_NT / 32];
-  T *acc = reinterpret_cast<T *>(smem_raw);
-  const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
-  const T UNT = Untouched<T>::value();
-  for (int c = tid; c < n; c += NT) acc[c] = UNT;
-  // columns per warp for the output sweep, a multiple of 32
-  const int cpw = ((n + nw - 1) / nw + 31) & ~31;
-  __syncthreads();
-
-// One B row: this thread's entry (index clamped, so the loads need no branch) ...
-#define OLD_FETCH(J, B, SG, Q)                                  \
-  {                                                               \
-    SG = s_seg[Q];                                                \
-    const int idx_ = SG.x + min(tid, max(SG.y - 1, 0));           \
-    J = __ldg(Bj + idx_);                                         \
-    B = __ldg(Bx + idx_);                                         \
-  }
-// ... applied in A-row order, one barrier per non-empty B row.
-#define OLD_APPLY(J, B, SG, Q)                                                         \
-  if (SG.y) { /* CTA-uniform */                                                          \
-    const T a_ = s_a[Q];                                                                 \
-    if (tid < SG.y) {                                                                    \
-      const T cur_ = acc[J];                                                             \
-      acc[J] = add_rn(Untouched<T>::is(cur_) ? T(0) : cur_, mul_rn(a_, B));              \
-    }                                                                                    \
-    if (SG.y > NT) { /* long B row: remaining strides, loaded in line */                 \
-      for (int u_ = tid + NT; u_ < SG.y; u_ += NT) {                                     \
-        const int j_ = __ldg(Bj + SG.x + u_);                                            \
-        const T cur_ = acc[j_];                                                          \
-        acc[j_] = add_rn(Untouched<T>::is(cur_) ? T(0) : cur_, mul_rn(a_, __ldg(Bx + SG.x + u_))); \
-      }                                                                                  \
-    }                                                                                    \
-    __syncthreads();                                                                     \
-  }
-
-  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
-    const int row = rows[ridx];
-    const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
-    for (int base = a_begin; base < a_end; base += NT) {
-      const int t = base + tid;
-      int2 sg = make_int2(0, 0);
-      T av = T(0);
-      if (t < a_end) {
-        const int kk = __ldg(Aj + t);
-        const int st = __ldg(Bp + kk);
-        sg.y = __ldg(Bp + kk + 1) - st;
-        sg.x = sg.y ? st : 0;  // empty rows of B point at a safe address
-        av = __ldg(Ax + t);
-      }
-      s_seg[tid] = sg;
-      s_a[tid] = av;
-      if (tid < OLD_PAD) s_seg[NT + tid] = make_int2(0, 0);
-      __syncthreads();
-      const int cnt = min(NT, a_end - base);  // entries [cnt, NT + PAD) have length 0
-      // rolling 4-deep register prefetch: the loads of B rows q+4.. are in flight while row q
-      // is applied, so the barrier chain does not wait on L2
-      int2 g0, g1, g2, g3;
-      int j0, j1, j2, j3;
-      T b0, b1, b2, b3;
-      OLD_FETCH(j0, b0, g0, 0)
-      OLD_FETCH(j1, b1, g1, 1)
-      OLD_FETCH(j2, b2, g2, 2)
-      OLD_FETCH(j3, b3, g3, 3)
-      for (int q = 0; q < cnt; q += 4) {
-        OLD_APPLY(j0, b0, g0, q)
-        OLD_FETCH(j0, b0, g0, q + 4)
-        OLD_APPLY(j1, b1, g1, q + 1)
-        OLD_FETCH(j1, b1, g1, q + 5)
-        OLD_APPLY(j2, b2, g2, q + 2)
-        OLD_FETCH(j2, b2, g2, q + 6)
-        OLD_APPLY(j3, b3, g3, q + 3)
-        OLD_FETCH(j3, b3, g3, q + 7)
-      }
-      __syncthreads();
-    }
-#undef OLD_FETCH
-#undef OLD_APPLY
-    // ---- output: warp w owns columns [w*cpw, (w+1)*cpw); count, prefix, then ordered emit ----
-    const int c_lo = min(w * cpw, n), c_hi = min(c_lo + cpw, n);
-    int mine = 0;
-    for (int c = c_lo; c < c_hi; c += 32) {
-      const bool touched = (c + lane < c_hi) && !Untouched<T>::is(acc[c + lane]);
-      mine += __popc(__ballot_sync(FULL, touched));
-    }
-    if (lane == 0) s_wcnt[w] = mine;
-    __syncthreads();
-    int pos = __ldg(Cp + row);
-    for (int q = 0; q < w; ++q) pos += s_wcnt[q];
-    for (int c = c_lo; c < c_hi; c += 32) {
-      T v = UNT;
-      if (c + lane < c_hi) v = acc[c + lane];
-      const bool touched = !Untouched<T>::is(v);
-      const unsigned bal = __ballot_sync(FULL, touched);
-      if (touched) {
-        const int o = pos + __popc(bal & ((1u << lane) - 1u));
-        Cj[o] = c + lane;
-        Cx[o] = scale_out(alpha, v);
-        acc[c + lane] = UNT;
-      }
-      pos += __popc(bal);
     }
     __syncthreads();
   }

@@ -97,6 +97,34 @@ def test_cancellation_keeps_explicit_zero(b200):
     assert p.tolist() == [0, 2] and j.tolist() == [0, 1] and x.tolist() == [0.0, 2.0]
 
 
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+@pytest.mark.parametrize("n,d", [(64, 0.3), (700, 0.2), (2048, 0.4)])
+def test_signed_zero_products_and_cancellation(b200, n, d, dt):
+    """Explicit zeros (+0.0 and -0.0) in A and B, signed values, exact cancellation: every bin
+    (incl. the dense accumulators, which mark untouched columns with a reserved bit pattern) must
+    keep the structural entries and give scipy's sign of zero (sums start at +0.0)."""
+    rng = np.random.default_rng(n)
+    A = helpers.random_csr(n, n, d, 31, dtype=dt)
+    B = helpers.random_csr(n, n, d, 32, dtype=dt)
+    for M in (A, B):
+        M.data[:] = rng.integers(-2, 3, M.nnz).astype(dt)          # small integers: many exact cancellations
+        M.data[rng.random(M.nnz) < 0.15] = dt(0.0)
+        M.data[rng.random(M.nnz) < 0.15] = dt(-0.0)
+    # a row of A made only of zeros against negative B values: all products are -0.0
+    A.data[A.indptr[3]:A.indptr[4]] = dt(0.0)
+    B.data[rng.random(B.nnz) < 0.3] *= dt(-1)
+    got = dev_spgemm(b200, A, B)
+    want = oracle_spgemm(A, B)
+    assert_csr_bitwise(got, want, f"signed zeros n={n}")
+    # scipy drops the entries that are exactly zero (csr_matmat: `if (sums[head] != 0)`);
+    # cuSPARSE and the product keep the structural pattern
+    C = (A @ B).tocsr()
+    C.sort_indices()
+    from oracle import oracle
+    assert_csr_bitwise(oracle.drop_zero_entries(got), (C.indptr, C.indices, C.data), "filtered vs scipy")
+    assert got[1].size > C.nnz
+
+
 def test_invalid_arguments(b200):
     """test_cusparse.py:413-453: TypeError for non-CSR operands, ValueError for bad shapes."""
     A = b200.csr_matrix(helpers.random_csr(4, 3, 0.5, 1))

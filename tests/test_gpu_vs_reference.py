@@ -82,3 +82,24 @@ def test_cli_chunk_fraction_argument_and_env(tmp_path):
     assert "chunk_fraction=0.1" in o2
     for f in ("indptr", "indices", "data"):   # twice-run cmp: deterministic/test_same.sh
         assert open(tmp_path / f"C1_{f}.txt").read() == open(tmp_path / f"C2_{f}.txt").read()
+
+
+def test_reference_driver_keeps_zero_sums(tmp_path):
+    """cuSPARSE (the reference's GPU path) keeps entries whose sum is exactly zero - the
+    structural pattern - where scipy drops them; the product follows cuSPARSE."""
+    ref_exe = os.path.join(REF, "spgemm_from_txt_alg1")
+    if not os.path.exists(ref_exe):
+        pytest.skip("oracle/_ref not built (reference checkout was absent at build time)")
+    import scipy.sparse as sp
+    A = sp.csr_matrix((np.array([1, 1, 0, 3], np.float32), np.array([0, 1, 0, 1]), np.array([0, 2, 4])), shape=(2, 2))
+    B = sp.csr_matrix((np.array([2, 1, -2, 1], np.float32), np.array([0, 1, 0, 1]), np.array([0, 2, 4])), shape=(2, 2))
+    pa, pb = str(tmp_path / "A"), str(tmp_path / "B")
+    _save(pa, A)
+    _save(pb, B)
+    _run(ref_exe, pa, pb, str(tmp_path / "C_cu"))
+    _run(os.path.join(OURS, "spgemm_from_txt_alg1"), pa, pb, str(tmp_path / "C_ours"))
+    rp, rj, rx = _load(str(tmp_path / "C_cu"))
+    op, oj, ox = _load(str(tmp_path / "C_ours"))
+    assert rp.tolist() == op.tolist() == [0, 2, 4] and rj.tolist() == oj.tolist() == [0, 1, 0, 1]
+    assert rx.tolist() == ox.tolist() == [0.0, 2.0, -6.0, 3.0]
+    assert (A @ B).nnz == 3     # scipy stores only the non-zero sums

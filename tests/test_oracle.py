@@ -164,3 +164,32 @@ def test_oracle_edge_cases():
     C = (A @ B).tocsr()
     C.sort_indices()
     helpers.assert_csr_bitwise(helpers.oracle_spgemm(A, B), helpers.triple(C), "skewed")
+
+
+def test_zero_sums_structural_vs_scipy():
+    """The one place SciPy and cuSPARSE differ: entries whose sum is exactly zero.  SciPy's second
+    pass skips them (`if (sums[head] != 0)`), cuSPARSE keeps the structural pattern.  The oracle
+    gives the structural form by default and SciPy's with drop_zeros=True."""
+    A = sp.csr_matrix(np.array([[1.0, 1.0]], np.float32))
+    B = sp.csr_matrix(np.array([[2.0, 1.0], [-2.0, 1.0]], np.float32))
+    p, j, x = oracle.spgemm(helpers.triple(A), helpers.triple(B), 2)
+    assert p.tolist() == [0, 2] and j.tolist() == [0, 1] and x.tolist() == [0.0, 2.0]
+    p, j, x = oracle.spgemm(helpers.triple(A), helpers.triple(B), 2, drop_zeros=True)
+    C = (A @ B).tocsr()
+    assert p.tolist() == C.indptr.tolist() == [0, 1] and j.tolist() == C.indices.tolist() == [1] and x.tolist() == [2.0]
+    # signed zeros, explicit zeros, small-integer values (many exact cancellations)
+    rng = np.random.default_rng(5)
+    for dt in (np.float32, np.float64):
+        A = helpers.random_csr(120, 90, 0.3, 31, dtype=dt)
+        B = helpers.random_csr(90, 150, 0.3, 32, dtype=dt)
+        for M in (A, B):
+            M.data[:] = rng.integers(-2, 3, M.nnz).astype(dt)
+            M.data[rng.random(M.nnz) < 0.15] = dt(-0.0)
+        full = oracle.spgemm(helpers.triple(A), helpers.triple(B), 150)
+        C = (A @ B).tocsr()
+        C.sort_indices()
+        helpers.assert_csr_bitwise(oracle.drop_zero_entries(full), (C.indptr, C.indices, C.data), "drop_zeros vs scipy")
+        assert full[1].size > C.nnz
+        # structural count = csr_matmat_maxnnz, SciPy's own first pass
+        ones = lambda M: sp.csr_matrix((np.ones(M.nnz), M.indices, M.indptr), shape=M.shape)  # noqa: E731
+        assert full[1].size == (ones(A) @ ones(B)).nnz
