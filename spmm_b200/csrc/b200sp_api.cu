@@ -467,7 +467,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       if (p.b_canonical && (size_t)p.n * sizeof(T) <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_BLOCKED_MAX) {
         const size_t budget = SMEM_BLOCKED_MAX;  // one CTA of 512 threads per SM
         const int nblk = (int)(((size_t)p.n * sizeof(T) + budget - 1) / budget);
-        const int W = (((p.n + nblk - 1) / nblk) + 31) & ~31;
+        const int W = (((p.n + nblk - 1) / nblk) + 127) & ~127;  // whole 128-column groups (vector sweep)
         const size_t smem = (size_t)W * sizeof(T);
         if (p.bounds_nblk != nblk || p.bounds_W != W) {  // first numeric call of this plan / value type
           const size_t total = (size_t)p.k * (nblk + 1);

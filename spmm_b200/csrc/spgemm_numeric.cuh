@@ -517,7 +517,7 @@ __device__ __forceinline__ int dense_count(const T *acc, int c_lo, int c_hi, int
 // well-filled rows).
 template <typename T, bool SCALE>
 __device__ __forceinline__ void dense_emit_ballot(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ Cj,
-                                                  T *__restrict__ Cx, int pos, T alpha) {
+                                                  T *__restrict__ Cx, int pos, T alpha, int col0 = 0) {
   const T UNT = NegZero<T>::value();
   const unsigned below = (1u << lane) - 1u;
 #pragma unroll 4
@@ -527,7 +527,7 @@ __device__ __forceinline__ void dense_emit_ballot(T *acc, int c_lo, int c_hi, in
     const unsigned bal = __ballot_sync(FULL, touched);
     if (touched) {
       const int o = pos + __popc(bal & below);
-      Cj[o] = c;
+      Cj[o] = col0 + c;
       Cx[o] = SCALE ? mul_rn(alpha, v) : v;
       acc[c] = UNT;
     }
@@ -539,7 +539,7 @@ __device__ __forceinline__ void dense_emit_ballot(T *acc, int c_lo, int c_hi, in
 // scan of the per-lane counts gives its output offset; the accumulator is reset on the way.
 template <typename T, bool SCALE>
 __device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ Cj,
-                                           T *__restrict__ Cx, int pos, T alpha) {
+                                           T *__restrict__ Cx, int pos, T alpha, int col0 = 0) {
   const T UNT = NegZero<T>::value();
   for (int c = c_lo + 4 * lane; c < c_hi; c += 128) {
     T v[4];
@@ -563,7 +563,7 @@ __device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane,
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         if (t[e]) {
-          Cj[o] = c + e;
+          Cj[o] = col0 + c + e;
           Cx[o] = SCALE ? mul_rn(alpha, v[e]) : v[e];
           ++o;
         }
@@ -725,10 +725,10 @@ k_num_dense_blocked(const int *__restrict__ rows, int nrows, int n, int W, int n
   __shared__ int s_wcnt[NWARP];
   T *acc = reinterpret_cast<T *>(smem_raw);
   const int tid = threadIdx.x, lane = lane_id(), w = tid >> 5;
-  const T UNT = Untouched<T>::value();
+  const T UNT = NegZero<T>::value();  // as in k_num_dense_cta: -0.0 marks an untouched column
   for (int c = tid; c < W; c += NT) acc[c] = UNT;
   for (int c = tid; c < BLOCKED_CLAIM; c += NT) s_claim[c] = INT_MAX;
-  const int cpw = ((W + NWARP - 1) / NWARP + 31) & ~31;  // columns per warp in the sweep
+  const int cpw = ((W + NWARP - 1) / NWARP + 127) & ~127;  // columns per warp in the sweep (W is a multiple of 128)
   __syncthreads();
   for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
     const int row = rows[ridx];
@@ -790,15 +790,14 @@ k_num_dense_blocked(const int *__restrict__ rows, int nrows, int n, int W, int n
         for (int r0 = 0; r0 < total; r0 += NT) {
           bool pending = have;
           const int myq = q, myj = j - c0;
-          const T p = mul_rn(aval, bval);
+          const T p = add_rn(mul_rn(aval, bval), T(0));  // -0.0 -> +0.0
           const int slot = (int)(((unsigned)myj * 0x9E3779B1u) >> 19) & (BLOCKED_CLAIM - 1);
           fetch(r0 + NT + tid);
           while (true) {
             if (pending) atomicMin(&s_claim[slot], myq);
             __syncthreads();
             if (pending && s_claim[slot] == myq) {
-              const T cur = acc[myj];
-              acc[myj] = add_rn(Untouched<T>::is(cur) ? T(0) : cur, p);
+              acc[myj] = add_rn(acc[myj], p);
               pending = false;
               s_claim[slot] = INT_MAX;
             }
@@ -807,13 +806,10 @@ k_num_dense_blocked(const int *__restrict__ rows, int nrows, int n, int W, int n
         }
         __syncthreads();  // s_seg / s_a / s_pre are restaged
       }
-      // ---- sweep of the block: warp w owns columns [w*cpw, (w+1)*cpw) of it ----
-      const int wl = min(w * cpw, c1 - c0), wh = min(wl + cpw, c1 - c0);
-      int mine = 0;
-      for (int c = wl; c < wh; c += 32) {
-        const bool touched = (c + lane < wh) && !Untouched<T>::is(acc[c + lane]);
-        mine += __popc(__ballot_sync(FULL, touched));
-      }
+      // ---- sweep of the block: warp w owns columns [w*cpw, (w+1)*cpw) of it (the accumulator
+      //      columns past c1 - c0 are never touched) ----
+      const int wl = min(w * cpw, W), wh = min(wl + cpw, W);
+      const int mine = dense_count<T>(acc, wl, wh, lane);
       if (lane == 0) s_wcnt[w] = mine;
       __syncthreads();
       int pos = out, tot = 0;
@@ -822,19 +818,13 @@ k_num_dense_blocked(const int *__restrict__ rows, int nrows, int n, int W, int n
         if (q < w) pos += v;
         tot += v;
       }
-      if (mine) {  // warp-uniform
-        for (int c = wl; c < wh; c += 32) {
-          T v = UNT;
-          if (c + lane < wh) v = acc[c + lane];
-          const bool touched = !Untouched<T>::is(v);
-          const unsigned bal = __ballot_sync(FULL, touched);
-          if (touched) {
-            const int o = pos + __popc(bal & ((1u << lane) - 1u));
-            Cj[o] = c0 + c + lane;
-            Cx[o] = scale_out(alpha, v);
-            acc[c + lane] = UNT;
-          }
-          pos += __popc(bal);
+      if (mine) {  // warp-uniform; sparse ranges take 128 columns per step, well-filled ones 32
+        if (mine > ((wh - wl) >> 2)) {
+          if (alpha == T(1)) dense_emit_ballot<T, false>(acc, wl, wh, lane, Cj, Cx, pos, alpha, c0);
+          else dense_emit_ballot<T, true>(acc, wl, wh, lane, Cj, Cx, pos, alpha, c0);
+        } else {
+          if (alpha == T(1)) dense_emit<T, false>(acc, wl, wh, lane, Cj, Cx, pos, alpha, c0);
+          else dense_emit<T, true>(acc, wl, wh, lane, Cj, Cx, pos, alpha, c0);
         }
       }
       out += tot;

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Runs each headline case a few times so that `ncu` can list / capture the kernels.
 
-  python tools/profile_cases.py [case ...]   cases: c3_1e-4 c3_1e-3 c3_1e-2 c1 spmv c4_1e-1
+  python tools/profile_cases.py [case ...]   cases: c3_1e-4 c3_1e-3 c3_1e-2 c1 spmv c4_1e-1 rmat16
 """
 import os
 import sys
@@ -27,7 +27,9 @@ def main():
             for _ in range(reps):
                 spmm_b200.cusparse.spmv(a, x)
         else:
-            if c == "c1":
+            if c.startswith("rmat"):
+                A = bench.rmat_matrix(int(c[4:]))
+            elif c == "c1":
                 A = bench.profiler_matrix(4096, 4096, 1e-3)
             else:
                 kind, d = c.split("_")
