@@ -184,3 +184,46 @@ def _gpu_compute(alg, chunk_fraction, alpha):
         c = cusparse.spgemm(a, b, alpha=alpha, alg=alg, chunk_fraction=chunk_fraction)
         return c.indptr, c.indices, c.data
     return run
+
+
+def spmv_row_panels(A, x, shape, compute=None, gather=True):
+    """y = A @ x over all ranks: contiguous row panels of A balanced by nonzeros, x broadcast
+    from rank 0 (one dist.broadcast), no reduction; y panels concatenated on rank 0
+    (SURVEY.md section 8e).
+
+    A: host CSR triple on every rank; x: host vector on rank 0 (None elsewhere).
+    compute(panel_triple_on_device, x_on_device, (mp, n)) -> device y panel; default = the GPU path.
+    Returns y (numpy, length m) on rank 0 when gather=True (None elsewhere), else (r0, r1, y panel).
+    """
+    rank, world = dist.get_rank(), dist.get_world_size()
+    m, n = shape
+    Ap, Aj, Ax = A
+    backend = dist.get_backend()
+    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+    vdt = torch.float64 if np.asarray(Ax).dtype == np.float64 else torch.float32
+    xd = torch.from_numpy(np.ascontiguousarray(x)).to(device=dev, dtype=vdt).reshape(-1) if rank == 0 else \
+        torch.empty(n, dtype=vdt, device=dev)
+    if xd.numel() != n:
+        raise ValueError("dimension mismatch")
+    dist.broadcast(xd, src=0)
+    bounds = balanced_row_panels(np.diff(np.asarray(Ap)).astype(np.int64), world)
+    r0, r1 = bounds[rank], bounds[rank + 1]
+    pp, pj, px = slice_rows(Ap, Aj, Ax, r0, r1)
+    panel = tuple(torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (pp, pj, px))
+    if compute is None:
+        compute = _gpu_spmv
+    y = compute(panel, xd, (r1 - r0, n)).cpu().numpy()
+    if not gather:
+        return r0, r1, y
+    out = [None] * world if rank == 0 else None
+    dist.gather_object(y, out, dst=0)
+    return np.concatenate(out) if rank == 0 else None
+
+
+def _gpu_spmv(panel, xd, shape):
+    from . import cusparse
+    from .sparse import csr_matrix
+    mp, n = shape
+    a = csr_matrix((panel[2], panel[1], panel[0]), shape=(mp, n))
+    a._canonical = True
+    return cusparse.spmv(a, xd)

@@ -117,3 +117,49 @@ def test_split_rows_by_bound():
     ub = np.minimum(rp, 60)
     assert all(ub[a:b].sum() <= 70 for a, b in zip(cuts[:-1], cuts[1:]))
     assert multi.split_rows_by_bound(rp, 60, 3, 3) == [3]
+
+
+def _oracle_spmv(panel, xd, shape):
+    from oracle import oracle
+    return torch.from_numpy(oracle.spmv(tuple(t.numpy() for t in panel), xd.numpy()))
+
+
+def _spmv_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        A = helpers.random_csr(301, 170, 0.1, 9)
+        A.data[:] = np.arange(A.nnz) % 7 - 3.0          # a few heavy rows shift the split
+        x = np.random.default_rng(3).standard_normal(170).astype(np.float32) if rank == 0 else None
+        y = multi.spmv_row_panels(helpers.triple(A), x, A.shape, compute=_oracle_spmv)
+        r0, r1, yp = multi.spmv_row_panels(helpers.triple(A), x, A.shape, compute=_oracle_spmv, gather=False)
+        q.put((rank, y, (r0, r1, yp.size)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_spmv_row_panels_world2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_spmv_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = {}
+    for _ in range(2):
+        rank, y, info = q.get(timeout=90)
+        res[rank] = (y, info)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[1][0] is None
+    A = helpers.random_csr(301, 170, 0.1, 9)
+    A.data[:] = np.arange(A.nnz) % 7 - 3.0
+    x = np.random.default_rng(3).standard_normal(170).astype(np.float32)
+    from oracle import oracle
+    want = oracle.spmv(helpers.triple(A), x)
+    assert np.array_equal(res[0][0].view(np.uint32), want.view(np.uint32))   # only rank 0 held x
+    (a0, a1, n0), (b0, b1, n1) = res[0][1], res[1][1]
+    assert a0 == 0 and a1 == b0 and b1 == 301 and n0 == a1 and n1 == b1 - b0 and 0 < a1 < 301
