@@ -456,10 +456,9 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       if ((size_t)p.n * sizeof(T) <= SMEM_DENSE_MAX) {
         const size_t smem = (((size_t)p.n + 127) & ~(size_t)127) * sizeof(T);  // padded to whole 128-column groups
         const double avgB = p.k ? (double)p.nnzB / (double)p.k : 0.0;
-        int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
-        if (const char *e = getenv("B200SP_DENSE_NT")) nt = std::max(32, std::min(DENSE_MAX_NT, atoi(e) / 32 * 32));
+        const int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
         TRY(set_smem(h, k_num_dense_cta<T>, smem));
-        k_num_dense_cta<T><<<persistent_grid(cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, getenv("B200SP_DENSE_FLAGS") ? atoi(getenv("B200SP_DENSE_FLAGS")) : 0);
+        k_num_dense_cta<T><<<persistent_grid(cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha);
         return check_launch(h, "k_num_dense_cta");
       }
       // fp64 with n between the fp32 and fp64 budgets: column blocks

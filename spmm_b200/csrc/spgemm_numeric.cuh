@@ -374,28 +374,17 @@ k_num_bitmap_global(const int *__restrict__ rows, int nrows, int n, const int *_
 // ---- CTA per row, dense accumulator over the n columns in shared memory ---------------------
 // For matrices whose column count fits shared memory (n * sizeof(T) <= ~200 KB) and rows of C
 // with more than a few hundred entries: slot = column, so there is no hashing, no probing and
-// no sort - the output sweep walks the columns in order.  "Untouched" is a reserved NaN bit
-// pattern that arithmetic cannot produce (the hardware returns the canonical NaN for invalid
-// operations and NaN operands), so explicit zeros from cancellation stay stored and no flag
-// array or atomic is needed.  The A nonzeros are applied one B row at a time with a barrier
-// in between (columns inside a B row are distinct); loads of R consecutive B rows are issued
-// together so the barrier chain never waits on L2.
-template <typename T> struct Untouched;
-template <> struct Untouched<float> {
-  static __device__ __forceinline__ float value() { return __int_as_float(0xFFC0DEAD); }
-  static __device__ __forceinline__ bool is(float v) { return __float_as_int(v) == (int)0xFFC0DEAD; }
-};
-template <> struct Untouched<double> {
-  static __device__ __forceinline__ double value() { return __longlong_as_double(0xFFF8DEADBEEF0001LL); }
-  static __device__ __forceinline__ bool is(double v) { return __double_as_longlong(v) == (long long)0xFFF8DEADBEEF0001LL; }
-};
-
-// k_num_dense_cta marks an untouched column with -0.0 instead: every product is canonicalised
+// no sort - the output sweep walks the columns in order.  The A nonzeros are applied one B-row
+// piece at a time with a barrier in between (columns inside a B row are distinct), which keeps
+// the per-column order of the sums = A-row storage order.
+//
+// An untouched column holds -0.0 and every product is canonicalised
 // (p + 0.0 turns a -0.0 product into +0.0 and changes nothing else), so that
 //   (-0.0) + p' = (+0.0) + p   bit for bit,
 // the first add needs no special case, and an accumulator that has been touched can never be
-// -0.0 again (x + y = -0.0 only for x = y = -0.0).  The read-modify-write chain is then
-// LDS -> FADD -> STS with no compare / select in it.
+// -0.0 again (x + y = -0.0 only for x = y = -0.0): explicit zeros from cancellation stay stored,
+// no flag array or atomic is needed, and the read-modify-write chain is LDS -> FADD -> STS with no
+// compare / select in it.
 template <typename T> struct NegZero;
 template <> struct NegZero<float> {
   static __device__ __forceinline__ float value() { return __int_as_float((int)0x80000000); }
@@ -443,7 +432,7 @@ template <typename T> struct __align__(16) DenseSeg {
 // next fetch is read one step early, so nothing but the accumulator read itself waits on shared
 // memory.  The thread's index into a piece is clamped to the last entry of B, not to the piece:
 // lanes past its end load a neighbour's entry and discard it.
-template <typename T, int D, bool REORDER>
+template <typename T, int D>
 __device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const DenseSeg<T> *s_seg, int cnt, int tid,
                                                    const int *__restrict__ Bj, const T *__restrict__ Bx, int last) {
   int j[D], len[D];
@@ -470,10 +459,9 @@ __device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const De
       T cur = T(0);
       if (act) cur = *slot;
       const T prod = add_rn(mul_rn(a[s], b[s]), T(0));  // -0.0 -> +0.0
-      if (REORDER) DENSE_FETCH(s, q + D + s)
+      DENSE_FETCH(s, q + D + s)
       if (act) *slot = add_rn(cur, prod);
       if (piece) __syncthreads();
-      if (!REORDER) DENSE_FETCH(s, q + D + s)
     }
   }
 #undef DENSE_FETCH
@@ -578,7 +566,7 @@ __global__ void __launch_bounds__(DENSE_MAX_NT, 3)
 k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
                 const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
                 const int *__restrict__ Bj, const T *__restrict__ Bx, int nnzB, const int *__restrict__ Cp,
-                int *__restrict__ Cj, T *__restrict__ Cx, T alpha, int flags) {
+                int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
   extern __shared__ __align__(16) unsigned char smem_raw[];  // round_up(n, 128) accumulator columns
   __shared__ DenseSeg<T> s_seg[DENSE_CAP + DENSE_PAD];       // the staged pieces of the round
   __shared__ int s_wcnt[DENSE_MAX_NT / 32];
@@ -641,8 +629,7 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
           s_seg[cnt + tid] = z;
         }
         __syncthreads();
-        if (flags & 2) dense_apply_staged<T, DENSE_DEPTH, false>(acc, s_seg, cnt, tid, Bj, Bx, nnzB - 1);
-        else dense_apply_staged<T, DENSE_DEPTH, true>(acc, s_seg, cnt, tid, Bj, Bx, nnzB - 1);
+        dense_apply_staged<T, DENSE_DEPTH>(acc, s_seg, cnt, tid, Bj, Bx, nnzB - 1);
         __syncthreads();
       }
       if (total == 0) __syncthreads();  // s_scan is rewritten by the next chunk
@@ -656,7 +643,7 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
     // well-filled rows: 32 columns per step with fully coalesced stores; sparse rows: 128 columns
     // per step (a quarter of the instructions, stores strided by the fill)
     const int row_nnz = __ldg(Cp + row + 1) - __ldg(Cp + row);
-    if ((flags & 1) || (!(flags & 4) && row_nnz > (npad >> 2))) {
+    if (row_nnz > (npad >> 2)) {
       if (alpha == T(1)) dense_emit_ballot<T, false>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
       else dense_emit_ballot<T, true>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
     } else {
