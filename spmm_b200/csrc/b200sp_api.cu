@@ -31,8 +31,9 @@ namespace {
 constexpr size_t SMEM_MAX = 227 * 1024;      // opt-in dynamic shared memory per CTA on sm_100
 constexpr size_t SMEM_BITMAP_MAX = 200 * 1024;  // budget for an n-bit bitmap in shared memory
 constexpr size_t SMEM_DENSE_MAX = 208 * 1024;   // budget for an n-column dense accumulator
-constexpr size_t SMEM_BLOCKED_MAX = 176 * 1024;  // accumulator budget of k_num_dense_blocked (it has ~46 KB of static smem)
-constexpr int DENSE_BLOCKED_MAX_BLOCKS = 64;     // most column blocks k_num_dense_blocked may need
+constexpr size_t SMEM_BLOCKED_MAX = 100 * 1024;  // accumulator budget of k_num_dense_pieces: two CTAs per SM (measured best)
+constexpr int DENSE_BLOCKED_MAX_BLOCKS = 384;    // most column blocks it may need (R-MAT scale 22 in fp64: 328)
+constexpr int PIECES_NT = 256;                   // its CTA size = the longest piece of a B row applied per barrier
 constexpr int RANKBM_MAX_N = 32768;             // widest matrix for the bitmap-rank output of the warp bins
 
 struct Buffer {  // grow-only device buffer
@@ -75,7 +76,7 @@ struct b200sp_context {
   void *alloc_ctx = nullptr;
   Buffer ws;       // plan workspace (row lists, counters, scan tiles)
   Buffer ws2;      // global bitmap workspace of the heavy-row kernels
-  Buffer ws3;      // per-B-row column-block boundaries of k_num_dense_blocked
+  Buffer ws3;      // row ticket + per-B-row column-block boundaries of k_num_dense_pieces
   Buffer io[10];   // device staging of the *_host entry points
   void *pinned_out[3] = {nullptr, nullptr, nullptr};  // host staging of C (handle owned)
   size_t pinned_out_size[3] = {0, 0, 0};
@@ -464,23 +465,26 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       // fp64 with n between the fp32 and fp64 budgets: column blocks
     case NUM_DENSE_BLOCKED:
       if (p.b_canonical && (size_t)p.n * sizeof(T) <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_BLOCKED_MAX) {
-        const size_t budget = SMEM_BLOCKED_MAX;  // one CTA of 512 threads per SM
+        const size_t budget = SMEM_BLOCKED_MAX;  // two CTAs of 256 threads per SM
         const int nblk = (int)(((size_t)p.n * sizeof(T) + budget - 1) / budget);
-        const int W = (((p.n + nblk - 1) / nblk) + 127) & ~127;  // whole 128-column groups (vector sweep)
-        const size_t smem = (size_t)W * sizeof(T);
+        const int W = (((p.n + nblk - 1) / nblk) + 127) & ~127;  // whole 128-column groups
+        const size_t smem = (size_t)W * sizeof(T) + (size_t)(W / 32) * 4;  // accumulators + touched-column bitmap
         if (p.bounds_nblk != nblk || p.bounds_W != W) {  // first numeric call of this plan / value type
           const size_t total = (size_t)p.k * (nblk + 1);
-          TRY(ensure(h, h->ws3, total * sizeof(int)));
+          TRY(ensure(h, h->ws3, 256 + total * sizeof(int)));  // [row ticket | pad | table]
           const int bgrid = (int)std::max<size_t>(1, std::min<size_t>((total + 255) / 256, (size_t)NUM_SMS * 16));
-          k_block_bounds<<<bgrid, 256, 0, st>>>(p.k, nblk, W, p.Bp, p.Bj, (int *)h->ws3.ptr);
+          k_block_bounds<<<bgrid, 256, 0, st>>>(p.k, nblk, W, p.Bp, p.Bj, (int *)h->ws3.ptr + 64);
           TRY(check_launch(h, "k_block_bounds"));
           p.bounds_nblk = nblk;
           p.bounds_W = W;
         }
-        TRY(set_smem(h, k_num_dense_blocked<T>, smem));
-        const int grid = std::max(1, std::min(cnt, NUM_SMS));
-        k_num_dense_blocked<T><<<grid, BLOCKED_NT, smem, st>>>(rows, cnt, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
-        return check_launch(h, "k_num_dense_blocked");
+        TRY(set_smem(h, k_num_dense_pieces<T, PIECES_NT>, smem));
+        int per_sm = 1;
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_dense_pieces<T, PIECES_NT>, PIECES_NT, smem));
+        const int grid = std::max(1, std::min(cnt, NUM_SMS * std::max(1, per_sm)));
+        CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, sizeof(int), st));  // rows are handed out by ticket
+        k_num_dense_pieces<T, PIECES_NT><<<grid, PIECES_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha);
+        return check_launch(h, "k_num_dense_pieces");
       }
       // B not canonical (or absurdly wide): the global-memory kernel takes any input
     case NUM_GLOBAL: {

@@ -654,22 +654,12 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
   }
 }
 
-// For matrices too wide for k_num_dense_cta (n * sizeof(T) > shared memory) and rows of C with
-// many entries: the n columns are cut into nblk blocks of W columns; for each block the CTA
-// walks the A row once and applies only the part of every B row that falls into the block (B
-// rows are sorted, so that part is one segment, found by binary search while a chunk of A
-// nonzeros is staged), then sweeps the W accumulators in order.  Blocks are processed left to
-// right, so the row's output is simply appended block after block: sorted, no hash table, no
-// sort, no global-memory accumulator.
-// Power-law inputs have thousands of SHORT segments per row, so the barrier-per-B-row scheme of
-// k_num_dense_cta would idle: instead the staged segments are flattened into one product stream
-// (prefix sum of the segment lengths, load-balanced search) that the CTA consumes NT products
-// per round.  Order per column is kept by a claim table: every pending product does
-// atomicMin(claim[hash(col)], q) with q its position in the A row; after a barrier only the
-// products that hold the minimum of their slot are applied (equal q means the same B row,
-// hence distinct columns), the others retry in the next sub-round.  Collisions are rare, so a
-// round costs ~2 barriers for NT products whatever the segment lengths.
-// Requires canonical B (the host checks).
+// ---- wide matrices (n * sizeof(T) > shared memory): column blocks -----------------------------
+// The n columns are cut into nblk blocks of W accumulators; for each block the CTA walks the A
+// row once and applies only the part of every B row that falls into the block (B rows are
+// sorted, so that part is one segment), then sweeps the block.  Blocks are processed left to
+// right, so the row's output is appended block after block: sorted, no hash table, no sort, no
+// global-memory accumulator.  Requires canonical B (the host checks).
 // bounds[kk*(nblk+1) + b] = first entry of B row kk with column >= b*W (b = 0..nblk; the last is
 // the row end): the segment of row kk inside column block b is [bounds[..b], bounds[..b+1]).
 // Built once per plan and value type; k*(nblk+1) ints of workspace.
@@ -694,124 +684,202 @@ k_block_bounds(int k, int nblk, int W, const int *__restrict__ Bp, const int *__
   }
 }
 
-constexpr int BLOCKED_NT = 512;
-constexpr int BLOCKED_CLAIM = 8192;  // claim slots (power of two)
+// k_num_dense_pieces: one B-row PIECE per barrier, pipelined.
+// The heavy rows of power-law inputs multiply A entries that point at hub rows of B, so their
+// segments inside a column block are long (R-MAT scale 16 / 18: 130 / 105 products per piece of
+// at most 256): the scheme of k_num_dense_cta - one piece of one B row per barrier step, columns
+// inside a piece distinct, order = A-row order for free, (column, value) loads 16 pieces ahead -
+// needs no search, no conflict handling and no retry.  Two earlier designs that flattened the
+// segments into a product stream (a claim table with CTA-wide retries; owner warps fed by a
+// stable counting sort) spent 10 warp instructions per product on search and ordering and were
+// 1.4-1.9x slower at scale 16-18 (profiles/r01_heavy_row_kernels.md).
+// Touched columns are recorded in a bitmap (one ATOMS.OR on the first touch of a column, found by
+// the -0.0 marker), so the per-block sweep reads W/32 words instead of W accumulators: lane l
+// takes word l of a group of 32, a warp scan of the popcounts gives its output offset, and it
+// walks its own set bits (sorted output; sparse rows pay for their entries, not for the block
+// width).
+constexpr int BLOCKED_DEPTH = 16;             // pieces whose loads are in flight (an L2 round trip is ~8 barrier steps)
+constexpr int BLOCKED_PAD = 2 * BLOCKED_DEPTH;  // zero-length staging entries after the last piece
 
-template <typename T>
-__global__ void __launch_bounds__(BLOCKED_NT, 1)
-k_num_dense_blocked(const int *__restrict__ rows, int nrows, int n, int W, int nblk,
-                    const int *__restrict__ Ap, const int *__restrict__ Aj, const T *__restrict__ Ax,
-                    const int *__restrict__ bounds, const int *__restrict__ Bj, const T *__restrict__ Bx,
-                    const int *__restrict__ Cp, int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
-  constexpr int NT = BLOCKED_NT, NWARP = NT / 32;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ int2 s_seg[NT];      // {start, len} of the staged B-row segments
-  __shared__ T s_a[NT];           // their A values
-  __shared__ int s_pre[NT + 1];   // exclusive prefix of the segment lengths
-  __shared__ int s_claim[BLOCKED_CLAIM];
-  __shared__ int s_wcnt[NWARP];
+template <typename T, int D>
+__device__ __forceinline__ void blocked_apply_staged(T *__restrict__ acc, unsigned *__restrict__ bm,
+                                                     const DenseSeg<T> *s_seg, int cnt, int tid, int c0,
+                                                     const int *__restrict__ Bj, const T *__restrict__ Bx, int last) {
+  // only the loaded (column, value) pairs ride in registers; length and A value of a piece are
+  // read back from the staging entry one step before its turn
+  int j[D];
+  T b[D];
+  DenseSeg<T> nx = s_seg[0];
+#define BLOCKED_FETCH(S, Q)                     \
+  {                                             \
+    const int idx_ = min(nx.start + tid, last); \
+    nx = s_seg[(Q) + 1];                        \
+    j[S] = ld_inplace(Bj + idx_);               \
+    b[S] = ld_inplace(Bx + idx_);               \
+  }
+#pragma unroll
+  for (int s = 0; s < D; ++s) BLOCKED_FETCH(s, s)
+  DenseSeg<T> cu = s_seg[0];
+  for (int q = 0; q < cnt; q += D) {
+#pragma unroll
+    for (int s = 0; s < D; ++s) {
+      const int len = cu.len;
+      const T a = cu.a;
+      cu = s_seg[q + s + 1];
+      const bool piece = len != 0;  // CTA-uniform; only the padding after the last piece is empty
+      const bool act = tid < len;
+      const int lc = j[s] - c0;
+      T cur = T(0);
+      if (act) cur = acc[lc];
+      const T prod = add_rn(mul_rn(a, b[s]), T(0));  // -0.0 -> +0.0
+      BLOCKED_FETCH(s, q + D + s)
+      if (act) {
+        acc[lc] = add_rn(cur, prod);
+        if (NegZero<T>::is(cur)) atomicOr(bm + (lc >> 5), 1u << (lc & 31));
+      }
+      if (piece) __syncthreads();
+    }
+  }
+#undef BLOCKED_FETCH
+}
+
+template <typename T, int NT>
+__global__ void __launch_bounds__(NT, 1)
+k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ticket, int n, int W, int nblk,
+                   const int *__restrict__ Ap, const int *__restrict__ Aj, const T *__restrict__ Ax,
+                   const int *__restrict__ bounds, const int *__restrict__ Bj, const T *__restrict__ Bx,
+                   int nnzB, const int *__restrict__ Cp, int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
+  constexpr int NW = NT / 32, CAP = 2 * NT;
+  extern __shared__ __align__(16) unsigned char smem_raw[];  // W accumulators, then W/32 bitmap words
+  __shared__ DenseSeg<T> s_seg[CAP + BLOCKED_PAD];
+  __shared__ int s_scan[NW];
+  __shared__ int s_gcnt[64];  // touched columns per group of 1024 (W <= 65536)
+  __shared__ int s_ticket;
   T *acc = reinterpret_cast<T *>(smem_raw);
+  unsigned *bm = reinterpret_cast<unsigned *>(smem_raw + (size_t)W * sizeof(T));
   const int tid = threadIdx.x, lane = lane_id(), w = tid >> 5;
-  const T UNT = NegZero<T>::value();  // as in k_num_dense_cta: -0.0 marks an untouched column
+  const int nwords = W >> 5;  // W is a multiple of 128
+  const T UNT = NegZero<T>::value();
   for (int c = tid; c < W; c += NT) acc[c] = UNT;
-  for (int c = tid; c < BLOCKED_CLAIM; c += NT) s_claim[c] = INT_MAX;
-  const int cpw = ((W + NWARP - 1) / NWARP + 127) & ~127;  // columns per warp in the sweep (W is a multiple of 128)
+  for (int c = tid; c < nwords; c += NT) bm[c] = 0u;
+  const int ngrp = (nwords + 31) >> 5;
   __syncthreads();
-  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
+  // rows are handed out by a global ticket: heavy rows differ 1000-fold in work, a fixed
+  // round-robin deal left the slowest CTA 1.2-1.35x behind the mean (R-MAT scale 16-18)
+  while (true) {
+    if (tid == 0) s_ticket = atomicAdd(ticket, 1);
+    __syncthreads();
+    const int ridx = s_ticket;  // the next write is behind the barriers of this row's blocks
+    if (ridx >= nrows) break;
     const int row = rows[ridx];
     const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
     int out = __ldg(Cp + row);
     for (int cb = 0; cb < nblk; ++cb) {
-      const int c0 = cb * W, c1 = min(n, c0 + W);
+      const int c0 = cb * W;
       for (int base = a_begin; base < a_end; base += NT) {
-        // ---- stage up to NT A nonzeros: the segment of their B row inside [c0, c1) ----
+        // ---- stage: thread t takes A nonzero base+t; the segment of its B row inside the block is
+        //      cut into pieces of <= NT entries, slots from an exclusive scan of the piece counts
         const int t = base + tid;
-        int2 sg = make_int2(0, 0);
+        int start = 0, len = 0;
         T av = T(0);
         if (t < a_end) {
           const int kk = __ldg(Aj + t);
           const int *bd = bounds + (size_t)kk * (nblk + 1) + cb;
-          const int lo = __ldg(bd), hi = __ldg(bd + 1);
-          sg = make_int2(lo, hi - lo);
+          start = __ldg(bd);
+          len = __ldg(bd + 1) - start;
           av = __ldg(Ax + t);
         }
-        s_seg[tid] = sg;
-        s_a[tid] = av;
-        // exclusive prefix of the lengths
-        int incl = sg.y;
+        const int pieces = (len + NT - 1) / NT;
+        int inc = pieces;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-          const int v = __shfl_up_sync(FULL, incl, o);
-          if (lane >= o) incl += v;
+          const int u = __shfl_up_sync(FULL, inc, o);
+          if (lane >= o) inc += u;
         }
-        if (lane == 31) s_wcnt[w] = incl;
+        if (lane == 31) s_scan[w] = inc;
         __syncthreads();
-        int wbase = 0;
-        for (int q = 0; q < w; ++q) wbase += s_wcnt[q];
-        s_pre[tid + 1] = wbase + incl;
-        if (tid == 0) s_pre[0] = 0;
-        __syncthreads();
-        const int total = s_pre[NT];
-        // ---- consume the product stream, NT products per round; the loads of round r+1 are
-        //      issued before round r is resolved ----
-        int q = 0, j = 0;
-        T bval = T(0), aval = T(0);
-        bool have = false;
-        auto fetch = [&](int e) {  // locate product e of the stream and request its column / value
-          have = e < total;
-          if (have) {
-            int lo = 0, hi = NT;  // largest q with s_pre[q] <= e
-            while (hi - lo > 1) {
-              const int mid = (lo + hi) >> 1;
-              if (s_pre[mid] <= e) lo = mid;
-              else hi = mid;
-            }
-            q = lo;
-            const int idx = s_seg[q].x + (e - s_pre[q]);
-            j = __ldg(Bj + idx);
-            bval = __ldg(Bx + idx);
-            aval = s_a[q];
-          }
-        };
-        fetch(tid);
-        for (int r0 = 0; r0 < total; r0 += NT) {
-          bool pending = have;
-          const int myq = q, myj = j - c0;
-          const T p = add_rn(mul_rn(aval, bval), T(0));  // -0.0 -> +0.0
-          const int slot = (int)(((unsigned)myj * 0x9E3779B1u) >> 19) & (BLOCKED_CLAIM - 1);
-          fetch(r0 + NT + tid);
-          while (true) {
-            if (pending) atomicMin(&s_claim[slot], myq);
-            __syncthreads();
-            if (pending && s_claim[slot] == myq) {
-              acc[myj] = add_rn(acc[myj], p);
-              pending = false;
-              s_claim[slot] = INT_MAX;
-            }
-            if (__syncthreads_count(pending) == 0) break;
-          }
+        int off = inc - pieces, total = 0;
+#pragma unroll
+        for (int q = 0; q < NW; ++q) {
+          const int v = s_scan[q];
+          if (q < w) off += v;
+          total += v;
         }
-        __syncthreads();  // s_seg / s_a / s_pre are restaged
+        for (int r0 = 0; r0 < total; r0 += CAP) {
+          const int cnt = min(CAP, total - r0);
+          const int p_lo = max(0, r0 - off), p_hi = min(pieces, r0 + CAP - off);
+          for (int pc = p_lo; pc < p_hi; ++pc) {
+            DenseSeg<T> sg;
+            sg.start = start + pc * NT;
+            sg.len = min(NT, len - pc * NT);
+            sg.a = av;
+            s_seg[off + pc - r0] = sg;
+          }
+          if (tid < BLOCKED_PAD) {
+            DenseSeg<T> z;
+            z.start = 0;
+            z.len = 0;
+            z.a = T(0);
+            s_seg[cnt + tid] = z;
+          }
+          __syncthreads();
+          blocked_apply_staged<T, BLOCKED_DEPTH>(acc, bm, s_seg, cnt, tid, c0, Bj, Bx, nnzB - 1);
+          __syncthreads();
+        }
+        if (total == 0) __syncthreads();  // s_scan is rewritten by the next chunk
       }
-      // ---- sweep of the block: warp w owns columns [w*cpw, (w+1)*cpw) of it (the accumulator
-      //      columns past c1 - c0 are never touched) ----
-      const int wl = min(w * cpw, W), wh = min(wl + cpw, W);
-      const int mine = dense_count<T>(acc, wl, wh, lane);
-      if (lane == 0) s_wcnt[w] = mine;
+      // ---- sweep of the block through the bitmap.  Groups of 32 words (1024 columns) are dealt
+      //      to the warps round-robin (power-law columns crowd the low indices: contiguous ranges
+      //      would leave one warp with most of the entries); count per group, prefix, ordered emit
+      for (int g = w; g < ngrp; g += NW) {
+        const int i = (g << 5) + lane;
+        const int c = warp_sum(i < nwords ? __popc(bm[i]) : 0);
+        if (lane == 0) s_gcnt[g] = c;
+      }
       __syncthreads();
-      int pos = out, tot = 0;
-      for (int q = 0; q < NWARP; ++q) {
-        const int v = s_wcnt[q];
-        if (q < w) pos += v;
-        tot += v;
+      const int g0 = lane < ngrp ? s_gcnt[lane] : 0, g1 = lane + 32 < ngrp ? s_gcnt[lane + 32] : 0;
+      int inc0 = g0, inc1 = g1;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u0 = __shfl_up_sync(FULL, inc0, o), u1 = __shfl_up_sync(FULL, inc1, o);
+        if (lane >= o) inc0 += u0, inc1 += u1;
       }
-      if (mine) {  // warp-uniform; sparse ranges take 128 columns per step, well-filled ones 32
-        if (mine > ((wh - wl) >> 2)) {
-          if (alpha == T(1)) dense_emit_ballot<T, false>(acc, wl, wh, lane, Cj, Cx, pos, alpha, c0);
-          else dense_emit_ballot<T, true>(acc, wl, wh, lane, Cj, Cx, pos, alpha, c0);
+      const int tot0 = __shfl_sync(FULL, inc0, 31), tot = tot0 + __shfl_sync(FULL, inc1, 31);
+      const int ex0 = inc0 - g0, ex1 = tot0 + inc1 - g1;  // exclusive prefix of groups lane and lane + 32
+      for (int g = w; g < ngrp; g += NW) {
+        const int gbase = __shfl_sync(FULL, g < 32 ? ex0 : ex1, g & 31);
+        const int gcnt = __shfl_sync(FULL, g < 32 ? g0 : g1, g & 31);
+        if (gcnt == 0) continue;  // warp-uniform
+        const int i = (g << 5) + lane;
+        unsigned word = i < nwords ? bm[i] : 0u;
+        const int c = __popc(word);
+        int inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int u = __shfl_up_sync(FULL, inc, o);
+          if (lane >= o) inc += u;
+        }
+        if (word) bm[i] = 0u;
+        int *cj = Cj + (out + gbase + inc - c);
+        T *cx = Cx + (out + gbase + inc - c);
+        T *ac = acc + (i << 5);
+        const int colbase = c0 + (i << 5);
+        if (alpha == T(1)) {
+          while (word) {
+            const int bit = __ffs(word) - 1;
+            word &= word - 1;
+            *cx++ = ac[bit];
+            ac[bit] = UNT;
+            *cj++ = colbase + bit;
+          }
         } else {
-          if (alpha == T(1)) dense_emit<T, false>(acc, wl, wh, lane, Cj, Cx, pos, alpha, c0);
-          else dense_emit<T, true>(acc, wl, wh, lane, Cj, Cx, pos, alpha, c0);
+          while (word) {
+            const int bit = __ffs(word) - 1;
+            word &= word - 1;
+            *cx++ = mul_rn(alpha, ac[bit]);
+            ac[bit] = UNT;
+            *cj++ = colbase + bit;
+          }
         }
       }
       out += tot;
