@@ -743,6 +743,58 @@ __device__ __forceinline__ void blocked_apply_staged(T *__restrict__ acc, unsign
 #undef BLOCKED_FETCH
 }
 
+// mbarrier hand-off between the warps of a CTA (one arrival per phase): the release/acquire pair
+// orders the accumulator updates of consecutive windows of the product stream.
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, int parity) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(a), "r"(parity) : "memory");
+}
+
+// acc[col] += v for the active lanes of one window of the product stream; lanes that hold the same
+// column (products of different B rows) are chained in lane order (= stream order) by the lowest
+// lane.  `peers` = __match_any_sync over the columns (computed before the warp's turn).
+template <typename T>
+__device__ __forceinline__ void window_apply(T *__restrict__ acc, unsigned *__restrict__ bm, int col, bool act, T v,
+                                             unsigned peers, bool any_multi, int maxn) {
+  const int lane = lane_id();
+  const bool lead = act && (peers & ((1u << lane) - 1u)) == 0;
+  T cur = T(0);
+  if (lead) cur = acc[col];
+  T a = add_rn(cur, v);
+  if (any_multi) {  // warp-uniform
+    unsigned m = peers & (peers - 1);  // the members after the leader, lowest lane first
+    for (int r = 1; r < maxn; ++r) {
+      const int src = m ? __ffs(m) - 1 : lane;
+      const T vv = __shfl_sync(FULL, v, src);
+      if (lead && m) a = add_rn(a, vv);
+      m &= m - 1;
+    }
+  }
+  if (lead) {
+    acc[col] = a;
+    if (NegZero<T>::is(cur)) atomicOr(bm + (col >> 5), 1u << (col & 31));
+  }
+}
+
+// Chunks with fewer products per piece than this take the window path: a window of 32 products
+// costs ~420 cycles of hand-off chain, a piece ~340 cycles of barrier step (measured: R-MAT scale
+// 16/18 unchanged, scale 20 961 -> 827 ms, scale 22 16.3 -> 12.0 s; 64 and above lose at scale 16-18).
+constexpr int PIECES_FLAT_BELOW = 32;
+
 template <typename T, int NT>
 __global__ void __launch_bounds__(NT, 1)
 k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ticket, int n, int W, int nblk,
@@ -753,11 +805,21 @@ k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ti
   extern __shared__ __align__(16) unsigned char smem_raw[];  // W accumulators, then W/32 bitmap words
   __shared__ DenseSeg<T> s_seg[CAP + BLOCKED_PAD];
   __shared__ int s_scan[NW];
-  __shared__ int s_gcnt[64];  // touched columns per group of 1024 (W <= 65536)
+  __shared__ int s_scanp[NW];  // products per warp of the staged chunk
+  __shared__ int s_gcnt[64];   // touched columns per group of 1024 (W <= 65536)
   __shared__ int s_ticket;
+  __shared__ __align__(8) unsigned long long s_turn[NW];  // hand-off barriers of the window path
+  // the window path reuses the staging array: prefix of the segment lengths, start - prefix, A value
+  static_assert(sizeof(s_seg) >= (2 * NT + 2) * sizeof(int) + 8 + NT * sizeof(T), "staging alias");
+  int *f_pre = reinterpret_cast<int *>(s_seg);
+  int *f_sbase = f_pre + NT + 1;
+  T *f_a = reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(s_seg) + (((2 * NT + 1) * sizeof(int) + 7) & ~size_t(7)));
   T *acc = reinterpret_cast<T *>(smem_raw);
   unsigned *bm = reinterpret_cast<unsigned *>(smem_raw + (size_t)W * sizeof(T));
   const int tid = threadIdx.x, lane = lane_id(), w = tid >> 5;
+  if (tid < NW) mbar_init(&s_turn[tid], 1);
+  int gwin = 0;   // windows handed out so far (CTA-uniform): window g belongs to warp g % NW
+  int turns = 0;  // hand-offs this warp has consumed (phase of its barrier)
   const int nwords = W >> 5;  // W is a multiple of 128
   const T UNT = NegZero<T>::value();
   for (int c = tid; c < W; c += NT) acc[c] = UNT;
@@ -796,14 +858,77 @@ k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ti
           const int u = __shfl_up_sync(FULL, inc, o);
           if (lane >= o) inc += u;
         }
-        if (lane == 31) s_scan[w] = inc;
+        int incp = len;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int u = __shfl_up_sync(FULL, incp, o);
+          if (lane >= o) incp += u;
+        }
+        if (lane == 31) {
+          s_scan[w] = inc;
+          s_scanp[w] = incp;
+        }
         __syncthreads();
-        int off = inc - pieces, total = 0;
+        int off = inc - pieces, total = 0, poff = incp - len, P = 0;
 #pragma unroll
         for (int q = 0; q < NW; ++q) {
-          const int v = s_scan[q];
-          if (q < w) off += v;
-          total += v;
+          const int v = s_scan[q], vp = s_scanp[q];
+          if (q < w) off += v, poff += vp;
+          total += v, P += vp;
+        }
+        if (total > 0 && P < PIECES_FLAT_BELOW * total) {
+          // ---- window path: short segments.  The chunk's products form one stream (A order);
+          //      window i = products [32 i, 32 i + 32) is applied by ONE warp, same-column lanes
+          //      chained in lane order; the windows are applied strictly one after the other
+          //      (warp g % NW takes window g and is handed the turn by its predecessor through an
+          //      mbarrier), while location, loads and the column match of the following windows
+          //      run ahead on the other warps.
+          f_pre[tid] = poff;
+          f_sbase[tid] = start - poff;
+          f_a[tid] = av;
+          if (tid == 0) f_pre[NT] = P;
+          __syncthreads();
+          const int nwin = (P + 31) >> 5;
+          int i = (w - gwin) & (NW - 1);  // my first window of this chunk
+          int col = 0;
+          T prod = T(0);
+          bool act = false;
+          auto fetch = [&](int win) {
+            const int pp = (win << 5) + lane;
+            act = win < nwin && pp < P;
+            if (act) {
+              int lo = 0, hi = NT;  // largest q with f_pre[q] <= pp
+#pragma unroll
+              for (int st = 0; st < 8; ++st) {
+                const int mid = (lo + hi) >> 1;
+                if (f_pre[mid] <= pp) lo = mid;
+                else hi = mid;
+              }
+              const int idx = f_sbase[lo] + pp;
+              col = __ldg(Bj + idx) - c0;
+              prod = add_rn(mul_rn(f_a[lo], __ldg(Bx + idx)), T(0));  // -0.0 -> +0.0
+            }
+          };
+          fetch(i);
+          for (; i < nwin; i += NW) {
+            const int mycol = col;
+            const T myprod = prod;
+            const bool myact = act;
+            fetch(i + NW);  // the next window of this warp is located and requested before the wait
+            const unsigned peers = __match_any_sync(FULL, myact ? mycol : (-1 - lane));
+            const bool any_multi = __any_sync(FULL, myact && (peers & (peers - 1)));
+            const int maxn = any_multi ? __reduce_max_sync(FULL, __popc(peers)) : 1;
+            if (gwin + i > 0) {  // every window but the very first of the CTA waits for its predecessor
+              mbar_wait(&s_turn[w], turns & 1);
+              ++turns;
+            }
+            window_apply<T>(acc, bm, mycol, myact, myprod, peers, any_multi, maxn);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_turn[(w + 1) & (NW - 1)]);
+          }
+          gwin += nwin;
+          __syncthreads();
+          continue;
         }
         for (int r0 = 0; r0 < total; r0 += CAP) {
           const int cnt = min(CAP, total - r0);

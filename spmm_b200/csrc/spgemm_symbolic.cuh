@@ -86,7 +86,7 @@ k_sym_hash_cta(const int *__restrict__ rows, int nrows, int S, const int *__rest
 // SMEM = false: bitmap in the CTA's slice of the global workspace (any n); persistent grid.
 // The bitmap is zero on entry to every row: the count sweep clears what it counts.
 template <bool SMEM>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 k_sym_bitmap_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
                  const int *__restrict__ Aj, const int *__restrict__ Bp,
                  const int *__restrict__ Bj, int *__restrict__ Cp, unsigned *__restrict__ gws) {

@@ -109,3 +109,44 @@ def scipy_canonical_from_coo(row, col, val, shape):
     M.sum_duplicates()
     M.sort_indices()
     return M
+
+
+def hub_pair(seed=3, k=3000, n=200000, hubs=40, hub_len=6000, tail_len=12, hot_cols=4, dtype=np.float32):
+    """Power-law shaped pair for the column-blocked heavy-row kernel (n too wide for one
+    shared-memory accumulator): `hubs` rows of B with `hub_len` entries (long segments inside a
+    column block: the piece-per-barrier path) and the rest with `tail_len` entries (a handful per
+    block: the ordered window path); every B row also holds columns 0 .. hot_cols-1, so the same
+    accumulator is hit by every segment (the order of the sums is what the test is about).
+    A: heavy rows that mix hub and tail rows of B, plus a few rows made of tail rows only."""
+    rng = np.random.default_rng(seed)
+    rows, cols = [], []
+    for i in range(k):
+        L = hub_len if i < hubs else tail_len
+        c = np.unique(np.concatenate([np.arange(hot_cols), rng.integers(hot_cols, n, size=L)]))
+        rows.append(np.full(c.size, i))
+        cols.append(c)
+    rows, cols = np.concatenate(rows), np.concatenate(cols)
+    B = sp.csr_matrix((rng.standard_normal(rows.size).astype(dtype), (rows, cols)), shape=(k, n))
+    a_rows, a_cols = [], []
+    shapes = [(30, 300), (40, 0), (0, 2500), (5, 1200), (1, 700), (12, 2900), (0, 600), (40, 2960)]
+    for i, (nh, nt) in enumerate(shapes * 3):
+        c = np.concatenate([rng.choice(hubs, size=nh, replace=False), hubs + rng.choice(k - hubs, size=nt, replace=False)])
+        c = np.sort(c)
+        a_rows.append(np.full(c.size, i))
+        a_cols.append(c)
+    a_rows, a_cols = np.concatenate(a_rows), np.concatenate(a_cols)
+    A = sp.csr_matrix((rng.standard_normal(a_rows.size).astype(dtype), (a_rows, a_cols)), shape=(len(shapes) * 3, k))
+    A.sort_indices()
+    B.sort_indices()
+    return A, B
+
+
+def rmat_matrix(scale):
+    """R-MAT recipe of BASELINE config C5: the generator bench.py uses."""
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    import bench
+    return bench.rmat_matrix(scale)

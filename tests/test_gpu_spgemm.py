@@ -154,6 +154,29 @@ def test_all_bins_large_n(b200, dtype):
     assert len(used) >= 5, f"numeric bins hit: {used}"
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("alg,cf", [(1, 0.2), (3, 0.3)])
+def test_heavy_rows_hubs_and_hot_columns(b200, dtype, alg, cf):
+    """Column-blocked heavy-row kernel (n = 200 000): hub rows of B give long segments (one piece
+    per barrier), the tail rows a few entries per block (ordered windows), and columns 0-3 sit in
+    every B row, so each heavy output row sums thousands of products into the same accumulators -
+    any slip in the A-row order of those sums changes the low bits."""
+    A, B = helpers.hub_pair(dtype=dtype)
+    want = oracle_spgemm(A, B)
+    got = dev_spgemm(b200, A, B, alg=alg, chunk_fraction=cf)
+    assert_csr_bitwise(got, want, "hubs")
+    assert_csr_bitwise(dev_spgemm(b200, A, B, alg=alg, chunk_fraction=cf), got, "hubs rerun")
+
+
+def test_rmat16_bitwise(b200):
+    """R-MAT scale 16 A @ A (4.0e8 products, nnz(C) 1.6e8, n = 65 536 > one accumulator): the C5
+    recipe at the largest scale the oracle finishes in seconds."""
+    A = helpers.rmat_matrix(16)
+    want = oracle_spgemm(A, A)
+    got = dev_spgemm(b200, A, A)
+    assert_csr_bitwise(got, want, "rmat16")
+
+
 def test_all_bins_chunked(b200):
     A, B = helpers.skewed_pair(seed=11)
     assert_csr_bitwise(dev_spgemm(b200, A, B, alg=3, chunk_fraction=0.3), oracle_spgemm(A, B), "skewed alg3")
