@@ -122,9 +122,13 @@ def main():
         for alg in (1, 2, 3):
             try:
                 out = subprocess.run([EXE, path, str(alg), "0.2", str(args.reps)], capture_output=True, text=True, timeout=600)
-                rows.append(json.loads(out.stdout.strip().splitlines()[-1]))
+                row = json.loads(out.stdout.strip().splitlines()[-1])
+                row.setdefault("impl", "cusparse")
+                row.setdefault("alg", alg)
+                rows.append(row)
             except Exception as e:
-                rows.append({"impl": "cusparse", "alg": alg, "error": repr(e)})
+                tail = (out.stderr or out.stdout).strip().splitlines()[-1:] if "out" in locals() else []
+                rows.append({"impl": "cusparse", "alg": alg, "error": (tail[0] if tail else repr(e))[:200]})
         os.unlink(path)
         for alg in (1, 3):
             rows.append(ours(A, alg))
