@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
-"""Times A @ A on R-MAT inputs (the heavy-row numeric kernels) and checks the result bit for bit
-against the CPU oracle for the scales the oracle finishes in seconds.
+"""Times A @ A on R-MAT inputs (the heavy-row numeric kernel k_num_dense_pieces) and checks the
+result bit for bit against the CPU oracle for the scales the oracle finishes in seconds.
 
   python tools/heavy_ab.py [scale ...] [--f64] [--no-check] [--reps N]
 
@@ -56,8 +56,7 @@ def main():
                                        nthreads=oracle.num_threads())
             eq = bool(np.array_equal(Op, Cp) and np.array_equal(Oj, Cj) and
                       np.array_equal(Ox.view(np.uint8), Cx.view(np.uint8)))
-        out = {"scale": sc, "dtype": "f64" if f64 else "f32", "heavy": os.environ.get("B200SP_HEAVY", "default"),
-               "ms_median": float(np.median(ts)), "ms_min": float(np.min(ts)), "nnzC": int(Cp[-1]), "sha": sha,
+        out = {"scale": sc, "dtype": "f64" if f64 else "f32", "ms_median": float(np.median(ts)), "ms_min": float(np.min(ts)), "nnzC": int(Cp[-1]), "sha": sha,
                "oracle_equal": eq}
         if st is not None:
             out["ms_symbolic"] = getattr(st, "ms_symbolic", None)
