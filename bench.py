@@ -503,7 +503,8 @@ def run_rmat(args):
 
 
 def extras(args, spmm_b200, torch, dev, peak):
-    """Side numbers next to the headline: SpMV GB/s on C2 and the C3 density sweep (few reps)."""
+    """Side numbers next to the headline: SpMV GB/s on C2, the C3 density sweep and R-MAT A @ A at
+    scale 16 / 18 (few reps)."""
     out = {}
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
@@ -553,6 +554,17 @@ def extras(args, spmm_b200, torch, dev, peak):
             out[f"c3_d{d:g}"] = {"ms": ms, "gflops": 2 * prods / ms / 1e6, "products": prods}
         except Exception as e:
             out[f"c3_d{d:g}_error"] = repr(e)
+    for sc in (16, 18):  # C5 recipe at the scales one call holds (the scale-22 job is `--workload rmat --scale 22`)
+        try:
+            A = rmat_matrix(sc)
+            a = spmm_b200.csr_matrix(A)
+            a._canonical = True
+            prods = count_products(A, A)
+            ms = timed(lambda: spmm_b200.cusparse.spgemm(a, a), 3)
+            out[f"c5_rmat{sc}"] = {"ms": ms, "gflops": 2 * prods / ms / 1e6, "products": prods}
+            del a
+        except Exception as e:
+            out[f"c5_rmat{sc}_error"] = repr(e)
     return out
 
 
