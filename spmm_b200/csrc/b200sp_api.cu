@@ -353,10 +353,10 @@ void plan_bins(Plan &p) {
     for (int b = 0; b < 4; ++b) p.num_limits.limit[b] = dl[b];
     p.num_bins[3] = {NUM_DENSE, 0};
   } else if ((size_t)p.n * 8 <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_BLOCKED_MAX) {
-    // wide matrix: rows with at least ~n/64 entries are worth the column-block walk and go to the
+    // wide matrix: rows with at least ~n/128 entries are worth the column-block walk and go to the
     // column-blocked dense kernel; an 8 K-slot shared-memory hash keeps the rows below that (the
     // 16 K-slot table leaves one 8-warp CTA per SM: R-MAT scale 20 runs 10 % faster without it)
-    const int t_dense = std::max(512, std::min(6144, p.n / 64));
+    const int t_dense = std::max(512, std::min(6144, p.n / 128));
     int nb = 3;
     if (t_dense > 512) {
       p.num_limits.limit[nb] = t_dense;
