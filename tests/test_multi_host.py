@@ -33,6 +33,22 @@ def test_row_products_and_balanced_panels():
     assert b[0] == 0 and b[-1] == 2 and len(b) == 5
 
 
+def test_block_cyclic_panels_cover_rows_once():
+    rng = np.random.default_rng(5)
+    w = (rng.pareto(1.2, size=1000) * 50).astype(np.int64)
+    for parts, per in ((1, 1), (2, 4), (8, 4), (3, 5)):
+        dealt = multi.block_cyclic_panels(w, parts, per)
+        assert len(dealt) == parts
+        ranges = sorted(r for part in dealt for r in part)
+        assert ranges[0][0] == 0 and ranges[-1][1] == len(w)
+        assert all(ranges[i][1] == ranges[i + 1][0] for i in range(len(ranges) - 1))  # disjoint, no gap
+        assert all(len(part) <= per for part in dealt)
+        loads = [sum(int(w[a:b].sum()) for a, b in part) for part in dealt]
+        assert max(loads) <= w.sum() / parts + per * (w.max() + 1) + len(w)
+    # fewer rows than panels: empty panels are dropped
+    assert sum(len(p) for p in multi.block_cyclic_panels(np.array([3, 3]), 4, 4)) <= 2
+
+
 def test_slice_and_concat_roundtrip():
     M = helpers.random_csr(40, 30, 0.2, 4)
     bounds = [0, 7, 7, 25, 40]
