@@ -134,6 +134,23 @@ int b200sp_spgemm_host(b200sp_handle_t handle, int dtype, int64_t m, int64_t k, 
 /* releases arrays returned by b200sp_read_csr_txt */
 int b200sp_free_host(void *ptr);
 
+/* -------------------------------------------- host-side plumbing of the row-panel driver ---- */
+/* ("C panels D2H into one pinned host buffer at offsets from an exclusive
+ * scan of per-panel nnzC".)  The reference has no multi-GPU path; its single-GPU drivers copy C
+ * back with plain cudaMemcpy (spgemm_from_txt_alg1.cu:190-193).  These three calls let several
+ * processes (one per GPU) land their C panels in ONE host buffer - e.g. a POSIX shared-memory
+ * segment mapped by every rank - at DMA speed:
+ *   b200sp_host_register   page-locks [ptr, ptr+bytes) for this process (cudaHostRegister,
+ *                          portable), so device-to-host copies into it are asynchronous DMA;
+ *   b200sp_host_unregister undoes it;
+ *   b200sp_memcpy_async    cudaMemcpyAsync on a caller stream (NULL = the handle's second DMA
+ *                          queue, which runs beside the kernels of the handle's compute stream).
+ *                          kind: 0 = host to device, 1 = device to host. */
+int b200sp_host_register(void *ptr, size_t bytes);
+int b200sp_host_unregister(void *ptr);
+int b200sp_memcpy_async(b200sp_handle_t handle, void *dst, const void *src, size_t bytes, int kind,
+                        void *cuda_stream);
+
 /* ------------------------------------------------------------ SpMV / SpMM ---- */
 
 /*

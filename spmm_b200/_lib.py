@@ -51,6 +51,9 @@ SYMBOLS = [
      [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_int,
       ctypes.c_float, c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp), ctypes.POINTER(c_vp), i64p, i64p]),
     ("b200sp_free_host", ctypes.c_int, [c_vp]),
+    ("b200sp_host_register", ctypes.c_int, [c_vp, ctypes.c_size_t]),
+    ("b200sp_host_unregister", ctypes.c_int, [c_vp]),
+    ("b200sp_memcpy_async", ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_size_t, ctypes.c_int, c_vp]),
     ("b200sp_spmv", ctypes.c_int, [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     ("b200sp_spmm", ctypes.c_int,
      [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp]),
@@ -140,7 +143,22 @@ def handle(device):
     return h
 
 
-def stats(device):
+def new_handle(device):
+    """A private library handle (own plan + workspace): the row-panel driver keeps one per
+    sub-panel so that the symbolic plans of all panels stay alive until their numeric pass."""
+    hv = c_vp()
+    st = load().b200sp_create(ctypes.byref(hv), int(device))
+    if st != OK:
+        raise B200spError(st, "b200sp_create failed: no usable CUDA device (there is no CPU fallback)")
+    return hv
+
+
+def destroy_handle(h):
+    load().b200sp_destroy(h)
+
+
+def stats(device, h=None):
     s = Stats()
-    check(handle(device), load().b200sp_get_stats(handle(device), ctypes.byref(s)))
+    h = h or handle(device)
+    check(h, load().b200sp_get_stats(h, ctypes.byref(s)))
     return s

@@ -70,6 +70,7 @@ struct Plan {
 
 struct b200sp_context {
   int device = 0;
+  int num_sms = 148;  // queried at create (cudaDevAttrMultiProcessorCount); sizes every persistent grid
   cudaStream_t stream = nullptr;
   void *(*alloc_fn)(size_t, void *) = nullptr;
   void (*free_fn)(void *, void *) = nullptr;
@@ -89,6 +90,12 @@ struct b200sp_context {
   float ms_symbolic = 0.f, ms_numeric = 0.f;
   bool numeric_timed = false;
   Plan plan;
+  // SpMV kernel choice: longest row of the last matrix seen (keyed by indptr pointer and sizes; a
+  // stale hit only costs speed, never correctness)
+  const int *spmv_key_ap = nullptr;
+  int spmv_key_m = -1;
+  int64_t spmv_key_nnz = -1;
+  int spmv_max_row = 0;
   std::string err;
 };
 
@@ -184,6 +191,18 @@ int check_launch(b200sp_context *h, const char *what) {
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
 }  // namespace
 
 // =============================================================================== handle ====
@@ -217,11 +236,17 @@ extern "C" int b200sp_create(b200sp_handle_t *handle, int device) {
     if (cudaGetDevice(&device) != cudaSuccess) device = 0;
   }
   h->device = device;
-  if (cudaSetDevice(device) != cudaSuccess ||
+  DeviceGuard guard(device);  // the caller's current device is restored on return
+  int cur = -1;
+  if (cudaGetDevice(&cur) != cudaSuccess || cur != device ||
       cudaMallocHost((void **)&h->h_counters, sizeof(Counters)) != cudaSuccess) {
     cudaGetLastError();
     delete h;
     return B200SP_ERR_CUDA;
+  }
+  if (cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || h->num_sms <= 0) {
+    cudaGetLastError();
+    h->num_sms = 148;
   }
   for (auto &e : h->ev) cudaEventCreate(&e);
   cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
@@ -233,7 +258,7 @@ extern "C" int b200sp_create(b200sp_handle_t *handle, int device) {
 
 extern "C" int b200sp_release_workspace(b200sp_handle_t h) {
   if (!h) return B200SP_ERR_INVALID;
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   cudaStreamSynchronize(h->stream);
   release(h, h->ws);
   release(h, h->ws2);
@@ -245,6 +270,7 @@ extern "C" int b200sp_release_workspace(b200sp_handle_t h) {
 
 extern "C" int b200sp_destroy(b200sp_handle_t h) {
   if (!h) return B200SP_OK;
+  DeviceGuard guard(h->device);
   b200sp_release_workspace(h);
   for (int i = 0; i < 3; ++i)
     if (h->pinned_out[i]) cudaFreeHost(h->pinned_out[i]);
@@ -260,7 +286,13 @@ extern "C" int b200sp_destroy(b200sp_handle_t h) {
 
 extern "C" int b200sp_set_stream(b200sp_handle_t h, void *cuda_stream) {
   if (!h) return B200SP_ERR_INVALID;
-  h->stream = (cudaStream_t)cuda_stream;
+  if (h->stream != (cudaStream_t)cuda_stream) {
+    // the workspaces (and the plan's row lists) are reused by the next call: work still queued on
+    // the old stream must be done before anything on the new one may overwrite or free them
+    DeviceGuard guard(h->device);
+    cudaStreamSynchronize(h->stream);
+    h->stream = (cudaStream_t)cuda_stream;
+  }
   return B200SP_OK;
 }
 
@@ -312,18 +344,6 @@ extern "C" int b200sp_reset_stats(b200sp_handle_t h) {
 
 namespace {
 
-struct DeviceGuard {
-  int prev = -1;
-  explicit DeviceGuard(int dev) {
-    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
-    if (prev != dev) cudaSetDevice(dev);
-    else prev = -1;
-  }
-  ~DeviceGuard() {
-    if (prev >= 0) cudaSetDevice(prev);
-  }
-};
-
 void plan_bins(Plan &p) {
   const size_t bitmap_bytes = (size_t)((p.n + 31) / 32) * 4;
   // symbolic bins, by the upper bound ub = min(products, n) of nnz(C_i)
@@ -368,10 +388,10 @@ void plan_bins(Plan &p) {
   }
 }
 
-int persistent_grid(int nrows, size_t smem_bytes) {
+int persistent_grid(b200sp_context *h, int nrows, size_t smem_bytes) {
   int per_sm = smem_bytes ? (int)std::min<size_t>(8, SMEM_MAX / std::max<size_t>(smem_bytes, 1)) : 8;
   per_sm = std::max(per_sm, 1);
-  return std::max(1, std::min(nrows, NUM_SMS * per_sm));
+  return std::max(1, std::min(nrows, h->num_sms * per_sm));
 }
 
 int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
@@ -392,7 +412,7 @@ int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
     case SYM_CTA_HASH: {
       const size_t smem = (size_t)bp.S * 4;
       TRY(set_smem(h, k_sym_hash_cta, smem));
-      k_sym_hash_cta<<<persistent_grid(cnt, smem), 256, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp);
+      k_sym_hash_cta<<<persistent_grid(h, cnt, smem), 256, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp);
       return check_launch(h, "k_sym_hash_cta");
     }
     case SYM_CTA_BITMAP: {
@@ -400,7 +420,7 @@ int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
       const size_t fbytes = (size_t)((p.n + 3) / 4) * 4;  // one byte flag per column
       if (fbytes <= SMEM_BITMAP_MAX) {
         TRY(set_smem(h, k_sym_flags_cta, fbytes));
-        k_sym_flags_cta<<<persistent_grid(cnt, fbytes + 64), 256, fbytes, st>>>(rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp);
+        k_sym_flags_cta<<<persistent_grid(h, cnt, fbytes + 64), 256, fbytes, st>>>(rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp);
         return check_launch(h, "k_sym_flags_cta");
       }
       if (bytes <= SMEM_BITMAP_MAX) {
@@ -409,11 +429,11 @@ int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
         // resident warps, so a bitmap that leaves room for one or two CTAs per SM gets bigger CTAs
         const int per_sm = (int)std::max<size_t>(1, SMEM_MAX / (bytes + 64));
         const int nt = per_sm >= 4 ? 256 : per_sm >= 2 ? 512 : 1024;
-        k_sym_bitmap_cta<true><<<persistent_grid(cnt, bytes + 64), nt, bytes, st>>>(
+        k_sym_bitmap_cta<true><<<persistent_grid(h, cnt, bytes + 64), nt, bytes, st>>>(
             rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp, nullptr);
         return check_launch(h, "k_sym_bitmap_cta<smem>");
       }
-      int grid = std::max(1, std::min(cnt, 2 * NUM_SMS / p.num_chunks));
+      int grid = std::max(1, std::min(cnt, 2 * h->num_sms / p.num_chunks));
       TRY(ensure(h, h->ws2, (size_t)grid * bytes));
       CUDA_TRY(h, cudaMemsetAsync(h->ws2.ptr, 0, (size_t)grid * bytes, st));
       k_sym_bitmap_cta<false><<<grid, 1024, 0, st>>>(rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp,
@@ -451,7 +471,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
     case NUM_CTA_HASH: {
       const size_t smem = (size_t)bp.S * (sizeof(T) + 4);
       TRY(set_smem(h, k_num_hash_cta<T>, smem));
-      k_num_hash_cta<T><<<persistent_grid(cnt, smem + 2304), 256, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
+      k_num_hash_cta<T><<<persistent_grid(h, cnt, smem + 2304), 256, smem, st>>>(rows, cnt, bp.S, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha);
       return check_launch(h, "k_num_hash_cta");
     }
     case NUM_DENSE:
@@ -460,7 +480,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         const double avgB = p.k ? (double)p.nnzB / (double)p.k : 0.0;
         const int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
         TRY(set_smem(h, k_num_dense_cta<T>, smem));
-        k_num_dense_cta<T><<<persistent_grid(cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha);
+        k_num_dense_cta<T><<<persistent_grid(h, cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha);
         return check_launch(h, "k_num_dense_cta");
       }
       // fp64 with n between the fp32 and fp64 budgets: column blocks
@@ -473,7 +493,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         if (p.bounds_nblk != nblk || p.bounds_W != W) {  // first numeric call of this plan / value type
           const size_t total = (size_t)p.k * (nblk + 1);
           TRY(ensure(h, h->ws3, 256 + total * sizeof(int)));  // [row ticket | pad | table]
-          const int bgrid = (int)std::max<size_t>(1, std::min<size_t>((total + 255) / 256, (size_t)NUM_SMS * 16));
+          const int bgrid = (int)std::max<size_t>(1, std::min<size_t>((total + 255) / 256, (size_t)h->num_sms * 16));
           k_block_bounds<<<bgrid, 256, 0, st>>>(p.k, nblk, W, p.Bp, p.Bj, (int *)h->ws3.ptr + 64);
           TRY(check_launch(h, "k_block_bounds"));
           p.bounds_nblk = nblk;
@@ -482,7 +502,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         TRY(set_smem(h, k_num_dense_pieces<T, PIECES_NT>, smem));
         int per_sm = 1;
         CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_dense_pieces<T, PIECES_NT>, PIECES_NT, smem));
-        const int grid = std::max(1, std::min(cnt, NUM_SMS * std::max(1, per_sm)));
+        const int grid = std::max(1, std::min(cnt, h->num_sms * std::max(1, per_sm)));
         CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, sizeof(int), st));  // rows are handed out by ticket
         k_num_dense_pieces<T, PIECES_NT><<<grid, PIECES_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha);
         return check_launch(h, "k_num_dense_pieces");
@@ -490,7 +510,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       // B not canonical (or absurdly wide): the global-memory kernel takes any input
     case NUM_GLOBAL: {
       const size_t bytes = (size_t)((p.n + 31) / 32) * 8;  // bitmap + prefix
-      int grid = std::max(1, std::min(cnt, 2 * NUM_SMS / p.num_chunks));
+      int grid = std::max(1, std::min(cnt, 2 * h->num_sms / p.num_chunks));
       TRY(ensure(h, h->ws2, (size_t)grid * bytes));
       CUDA_TRY(h, cudaMemsetAsync(h->ws2.ptr, 0, (size_t)grid * bytes, st));
       k_num_bitmap_global<T><<<grid, 256, 0, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha, (unsigned *)h->ws2.ptr);
@@ -573,7 +593,7 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
   {
     const double avg = (double)nnzA / (double)m;
     const int G = avg <= 2 ? 2 : avg <= 6 ? 4 : avg <= 12 ? 8 : avg <= 24 ? 16 : 32;
-    const int grid = std::max(1, std::min((int)((m + 256 / G - 1) / (256 / G)), NUM_SMS * 8));
+    const int grid = std::max(1, std::min((int)((m + 256 / G - 1) / (256 / G)), h->num_sms * 8));
     switch (G) {
       case 2: k_row_products<2><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
       case 4: k_row_products<4><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
@@ -583,7 +603,16 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
     }
     TRY(check_launch(h, "k_row_products"));
   }
-  const int sgrid = std::max(1, std::min((p.m + 255) / 256, NUM_SMS * 8));
+  // Every numeric kernel applies one B row (or a piece of it) per ordered step and relies on the
+  // columns inside a B row being distinct; the column-blocked kernels also on their being sorted.
+  // One O(nnzB) pass verifies it (the precondition asserted at cupyx/cusparse.py:2030-2031); the
+  // flag comes back with the counters of sync #1.
+  if (nnzB > 0) {
+    const int cgrid = std::max(1, std::min((int)((k + 7) / 8), h->num_sms * 8));
+    k_csr_check_canonical<<<cgrid, 256, 0, st>>>(p.k, p.n, dBp, dBj, &ctr->b_bad);
+    TRY(check_launch(h, "k_csr_check_canonical"));
+  }
+  const int sgrid = std::max(1, std::min((p.m + 255) / 256, h->num_sms * 8));
   k_scatter_rows<false><<<sgrid, 256, 0, st>>>(p.m, rowub, p.sym_limits, ctr, p.rows_sym);
   TRY(check_launch(h, "k_scatter_rows<sym>"));
   // sync #1: product total + symbolic bin sizes
@@ -591,6 +620,10 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
   CUDA_TRY(h, cudaStreamSynchronize(st));
   if (h->h_counters->overflow)
     return fail(h, B200SP_ERR_OVERFLOW, "a row of A@B has more than 2^31-1 intermediate products");
+  if (h->h_counters->b_bad)
+    return fail(h, B200SP_ERR_INVALID,
+                "B is not canonical (a row has unsorted, duplicate or out-of-range column indices): "
+                "canonicalise it first (b200sp_csr_sum_duplicates / b200sp_csr_sort_indices)");
   p.num_products = (int64_t)h->h_counters->total_products;
   p.max_row_products = h->h_counters->max_row_products;
   if (num_products) *num_products = p.num_products;
@@ -622,21 +655,13 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
   }
   k_scatter_rows<true><<<sgrid, 256, 0, st>>>(p.m, dCp, p.num_limits, ctr, p.rows_num);
   TRY(check_launch(h, "k_scatter_rows<num>"));
-  // the column-blocked dense kernel relies on sorted B rows: verify (O(nnzB) reads) before using it
-  const bool need_canonical = p.num_bins[p.num_limits.nbins - 1].kind == NUM_DENSE_BLOCKED ||
-                              (p.num_bins[p.num_limits.nbins - 1].kind == NUM_DENSE);
-  if (need_canonical && nnzB > 0) {
-    const int cgrid = std::max(1, std::min((int)((k + 7) / 8), NUM_SMS * 8));
-    k_csr_check_canonical<<<cgrid, 256, 0, st>>>(p.k, p.n, dBp, dBj, &ctr->b_bad);
-    TRY(check_launch(h, "k_csr_check_canonical"));
-  }
   cudaEventRecord(h->ev[1], st);
   // sync #2: nnz(C) + numeric bin sizes (the reference's cusparseSpMatGetSize sync)
   CUDA_TRY(h, cudaMemcpyAsync(h->h_counters, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(h, cudaStreamSynchronize(st));
   cudaEventElapsedTime(&h->ms_symbolic, h->ev[0], h->ev[1]);
   p.nnzC = (int64_t)h->h_counters->nnz_c;
-  p.b_canonical = !h->h_counters->b_bad;
+  p.b_canonical = true;  // verified before sync #1
   for (int b = 0; b < p.num_limits.nbins; ++b) p.num_count[b] = h->h_counters->num_count[b];
   *nnzC = p.nnzC;
   if (p.nnzC > INT32_MAX)
@@ -674,9 +699,40 @@ int run_spmv(b200sp_context *h, int m, int n, int64_t nnz, int64_t ncols, const 
   const T b = beta ? *(const T *)beta : T(0);
   cudaStream_t st = h->stream;
   if (m == 0 || ncols == 0) return B200SP_OK;
-  const char *mode = getenv("B200SP_SPMV_KERNEL");  // "vector" forces the row-group kernel, "tile" the merge-path one
-  const bool want_stream = !(mode && strcmp(mode, "vector") == 0);
-  if (want_stream && ncols == 1 && nnz > 0) {
+  // Kernel choice.  Row-group ("vector") kernel with 128-bit loads for matrices whose rows are of
+  // similar length (C2: 67 us vs 75 us merge-path); merge-path when one row can hold a warp up
+  // (R-MAT scale 20, longest row 39 705: 89 us vs 1875 us).  The longest row is measured once per
+  // matrix (one small kernel + a 4-byte D2H) and cached on the handle.
+  // B200SP_SPMV_KERNEL = vector | merge forces one; "+scalar" (e.g. "merge+scalar") forces the
+  // 4-byte-load variants (what bench.py uses to report both).
+  const char *mode = getenv("B200SP_SPMV_KERNEL");
+  const bool force_vector = mode && strncmp(mode, "vector", 6) == 0;
+  const bool force_merge = mode && (strncmp(mode, "merge", 5) == 0 || strncmp(mode, "tile", 4) == 0);
+  const bool scalar_only = mode && strstr(mode, "scalar") != nullptr;
+  const bool aligned = (((uintptr_t)Aj | (uintptr_t)Ax) & 15) == 0;
+  const bool vec = aligned && !scalar_only;
+  bool use_merge = ncols == 1 && nnz > 0;
+  if (use_merge && force_vector) use_merge = false;
+  if (use_merge && !force_merge) {
+    if (h->spmv_key_ap != Ap || h->spmv_key_m != m || h->spmv_key_nnz != nnz) {
+      TRY(ensure(h, h->ws2, 256));
+      int *d_max = (int *)h->ws2.ptr;
+      CUDA_TRY(h, cudaMemsetAsync(d_max, 0, sizeof(int), st));
+      k_max_row_len<<<std::max(1, std::min((m + 255) / 256, h->num_sms * 8)), 256, 0, st>>>(m, Ap, d_max);
+      TRY(check_launch(h, "k_max_row_len"));
+      int mx = 0;
+      CUDA_TRY(h, cudaMemcpyAsync(&mx, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(h, cudaStreamSynchronize(st));
+      h->spmv_key_ap = Ap;
+      h->spmv_key_m = m;
+      h->spmv_key_nnz = nnz;
+      h->spmv_max_row = mx;
+    }
+    const double avg_len = (double)nnz / (double)m;
+    // a row-group kernel finishes when its longest row does: fine while that row is a few trips
+    use_merge = (double)h->spmv_max_row > 32.0 * avg_len + 512.0;
+  }
+  if (use_merge) {
     const long long total = (long long)m + nnz;  // merge items: row-end markers + nonzeros
     const int ntiles = (int)((total + SPMV_TILE - 1) / SPMV_TILE);
     const size_t o_i = align_up((size_t)(ntiles + 1) * sizeof(int), 256);
@@ -689,15 +745,30 @@ int run_spmv(b200sp_context *h, int m, int n, int64_t nnz, int64_t ncols, const 
     T *head = (T *)(base + o_h), *carry = (T *)(base + o_c);
     k_spmv_partition<<<(ntiles + 1 + 7) / 8, 256, 0, st>>>(m, total, ntiles, Ap, tile_row);
     TRY(check_launch(h, "k_spmv_partition"));
-    k_spmv_merge<T><<<ntiles, SPMV_THREADS, 0, st>>>(m, (int)nnz, tile_row, Ap, Aj, Ax, X, Y, a, b, info, head, carry);
+    if (vec) k_spmv_merge<T, true><<<ntiles, SPMV_THREADS, 0, st>>>(m, (int)nnz, tile_row, Ap, Aj, Ax, X, Y, a, b, info, head, carry);
+    else k_spmv_merge<T, false><<<ntiles, SPMV_THREADS, 0, st>>>(m, (int)nnz, tile_row, Ap, Aj, Ax, X, Y, a, b, info, head, carry);
     TRY(check_launch(h, "k_spmv_merge"));
     if (ntiles == 1) return B200SP_OK;  // no row can span tiles
     k_spmv_fixup<T><<<(ntiles + 255) / 256, 256, 0, st>>>(ntiles, info, head, carry, Y, a, b);
     return check_launch(h, "k_spmv_fixup");
   }
   const double avg = (double)nnz / (double)m;
+  if (vec) {  // four entries per lane and trip: a quarter of the lanes per row
+    const int G = avg <= 3 ? 1 : avg <= 6 ? 2 : avg <= 12 ? 4 : avg <= 24 ? 8 : avg <= 48 ? 16 : 32;
+    const int gx = std::max(1, std::min((int)(((int64_t)m + 256 / G - 1) / (256 / G)), h->num_sms * 16));
+    dim3 grid(gx, (unsigned)ncols);
+    switch (G) {
+      case 1: k_spmv_vector4<1, T><<<grid, 256, 0, st>>>(m, (int)nnz, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+      case 2: k_spmv_vector4<2, T><<<grid, 256, 0, st>>>(m, (int)nnz, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+      case 4: k_spmv_vector4<4, T><<<grid, 256, 0, st>>>(m, (int)nnz, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+      case 8: k_spmv_vector4<8, T><<<grid, 256, 0, st>>>(m, (int)nnz, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+      case 16: k_spmv_vector4<16, T><<<grid, 256, 0, st>>>(m, (int)nnz, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+      default: k_spmv_vector4<32, T><<<grid, 256, 0, st>>>(m, (int)nnz, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
+    }
+    return check_launch(h, "k_spmv_vector4");
+  }
   const int G = avg <= 3 ? 2 : avg <= 6 ? 4 : avg <= 12 ? 8 : avg <= 24 ? 16 : 32;
-  const int gx = std::max(1, std::min((int)(((int64_t)m + 256 / G - 1) / (256 / G)), NUM_SMS * 16));
+  const int gx = std::max(1, std::min((int)(((int64_t)m + 256 / G - 1) / (256 / G)), h->num_sms * 16));
   dim3 grid(gx, (unsigned)ncols);
   switch (G) {
     case 2: k_spmv_vector<2, T><<<grid, 256, 0, st>>>(m, Ap, Aj, Ax, X, ldx, Y, ldy, a, b); break;
@@ -748,7 +819,7 @@ extern "C" int b200sp_csr_is_canonical(b200sp_handle_t h, int64_t m, int64_t nco
   TRY(ensure(h, h->ws2, 256));
   int *flag = (int *)h->ws2.ptr;
   CUDA_TRY(h, cudaMemsetAsync(flag, 0, sizeof(int), h->stream));
-  const int grid = std::max(1, std::min((int)((m + 7) / 8), NUM_SMS * 8));
+  const int grid = std::max(1, std::min((int)((m + 7) / 8), h->num_sms * 8));
   k_csr_check_canonical<<<grid, 256, 0, h->stream>>>((int)m, (int)ncols, dAp, dAj, flag);
   TRY(check_launch(h, "k_csr_check_canonical"));
   int bad = 0;
@@ -771,7 +842,7 @@ extern "C" int b200sp_csr_sort_indices(b200sp_handle_t h, int dtype, int64_t m, 
   const size_t vs = dtype == B200SP_R_32F ? 4 : 8;
   const int cap = 16384;
   const size_t smem = (size_t)cap * (vs + 4);
-  const int grid = std::max(1, std::min((int)m, NUM_SMS * 2));
+  const int grid = std::max(1, std::min((int)m, h->num_sms * 2));
   if (dtype == B200SP_R_32F) {
     TRY(set_smem(h, k_csr_sort_rows<float>, smem));
     k_csr_sort_rows<float><<<grid, 256, smem, h->stream>>>((int)m, cap, dAp, dAj, (float *)dAx, flag);
@@ -915,5 +986,41 @@ extern "C" int b200sp_spmv_host(b200sp_handle_t h, int dtype, int64_t m, int64_t
 
 extern "C" int b200sp_free_host(void *ptr) {
   free(ptr);
+  return B200SP_OK;
+}
+
+// ---- plumbing of the row-panel driver (spmm_b200/multi.py): one shared host buffer for C ----
+
+extern "C" int b200sp_host_register(void *ptr, size_t bytes) {
+  if (!ptr || !bytes) return B200SP_ERR_INVALID;
+  const cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+  if (e == cudaErrorHostMemoryAlreadyRegistered) {
+    cudaGetLastError();
+    return B200SP_OK;
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? B200SP_ERR_ALLOC : B200SP_ERR_CUDA;
+  }
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_host_unregister(void *ptr) {
+  if (!ptr) return B200SP_ERR_INVALID;
+  if (cudaHostUnregister(ptr) != cudaSuccess) {
+    cudaGetLastError();
+    return B200SP_ERR_CUDA;
+  }
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_memcpy_async(b200sp_handle_t h, void *dst, const void *src, size_t bytes, int kind,
+                                   void *cuda_stream) {
+  if (!h || (kind != 0 && kind != 1)) return h ? fail(h, B200SP_ERR_INVALID, "bad argument") : B200SP_ERR_INVALID;
+  if (!bytes) return B200SP_OK;
+  if (!dst || !src) return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : (h->copy_stream ? h->copy_stream : h->stream);
+  CUDA_TRY(h, cudaMemcpyAsync(dst, src, bytes, kind == 0 ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, st));
   return B200SP_OK;
 }

@@ -13,7 +13,7 @@ namespace b200sp {
 
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int EMPTY = -1;  // empty hash slot (column indices are >= 0)
-constexpr int NUM_SMS = 148;
+
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 

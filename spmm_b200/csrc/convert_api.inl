@@ -85,8 +85,8 @@ int check_convert_args(b200sp_context *h, int dtype, int64_t m, int64_t n, int64
   return B200SP_OK;
 }
 
-inline int flat_grid(int64_t items, int per_cta) {
-  return (int)std::max<int64_t>(1, std::min<int64_t>((items + per_cta - 1) / per_cta, NUM_SMS * 16));
+inline int flat_grid(b200sp_context *h, int64_t items, int per_cta) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>((items + per_cta - 1) / per_cta, h->num_sms * 16));
 }
 
 // sorted keys + payload -> summed, duplicate-free CSR; one host sync for nnz_out and the input flag
@@ -101,7 +101,7 @@ int finish_unique(b200sp_context *h, SortScratch &s, int cur, int64_t m, int64_t
   TRY(dev_exscan(h, tile_heads, nt, s.sums, s.total));
   k_uniq_emit<T><<<nt, GS_THREADS, 0, st>>>(s.keys[cur], s.perm[cur], val, nnz, tile_heads, s.keys[cur ^ 1], Cj, Cx);
   TRY(check_launch(h, "k_uniq_emit"));
-  k_ptr_from_sorted<<<flat_grid(m + 1, 256), 256, 0, st>>>((int)m, s.keys[cur ^ 1], nnz, s.total, Cp);
+  k_ptr_from_sorted<<<flat_grid(h, m + 1, 256), 256, 0, st>>>((int)m, s.keys[cur ^ 1], nnz, s.total, Cp);
   TRY(check_launch(h, "k_ptr_from_sorted"));
   long long total = 0;
   int bad = 0;
@@ -119,7 +119,7 @@ int run_coo_to_csr(b200sp_context *h, int64_t m, int64_t n, int64_t nnz, const i
   SortScratch s;
   TRY(carve_sort_scratch(h, nnz, s));
   CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, sizeof(int), h->stream));
-  k_keys_from_coo<<<flat_grid(nnz, 1024), 256, 0, h->stream>>>(nnz, (int)m, (int)n, row, col, s.keys[0], s.flag);
+  k_keys_from_coo<<<flat_grid(h, nnz, 1024), 256, 0, h->stream>>>(nnz, (int)m, (int)n, row, col, s.keys[0], s.flag);
   TRY(check_launch(h, "k_keys_from_coo"));
   int cur = 0;
   TRY(radix_sort(h, s, nnz, bits_for(n), bits_for(m), &cur));
@@ -132,7 +132,7 @@ int run_csr_sum_duplicates(b200sp_context *h, int64_t m, int64_t n, int64_t nnz,
   SortScratch s;
   TRY(carve_sort_scratch(h, nnz, s));
   CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, sizeof(int), h->stream));
-  k_keys_from_compressed<true><<<flat_grid(m, 8), 256, 0, h->stream>>>((int)m, (int)n, nnz, Ap, Aj, s.keys[0], s.flag);
+  k_keys_from_compressed<true><<<flat_grid(h, m, 8), 256, 0, h->stream>>>((int)m, (int)n, nnz, Ap, Aj, s.keys[0], s.flag);
   TRY(check_launch(h, "k_keys_from_compressed"));
   int cur = 0;
   // the input is already grouped by row: sorting on the column digits and then on the row
@@ -149,16 +149,16 @@ int run_transpose(b200sp_context *h, int64_t nmajor, int64_t nminor, int64_t nnz
   TRY(carve_sort_scratch(h, nnz, s));
   cudaStream_t st = h->stream;
   CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, sizeof(int), st));
-  k_keys_from_compressed<false><<<flat_grid(nmajor, 8), 256, 0, st>>>((int)nmajor, (int)nminor, nnz, ptr, idx, s.keys[0],
+  k_keys_from_compressed<false><<<flat_grid(h, nmajor, 8), 256, 0, st>>>((int)nmajor, (int)nminor, nnz, ptr, idx, s.keys[0],
                                                                     s.flag);
   TRY(check_launch(h, "k_keys_from_compressed"));
   int cur = 0;
   // entries arrive in ascending major order, so a stable sort on the minor index alone leaves
   // every output segment sorted by the old major index
   TRY(radix_sort(h, s, nnz, 0, bits_for(nminor), &cur));
-  k_emit_sorted<T><<<flat_grid(nnz, 1024), 256, 0, st>>>(nnz, s.keys[cur], s.perm[cur], val, out_idx, out_val);
+  k_emit_sorted<T><<<flat_grid(h, nnz, 1024), 256, 0, st>>>(nnz, s.keys[cur], s.perm[cur], val, out_idx, out_val);
   TRY(check_launch(h, "k_emit_sorted"));
-  k_ptr_from_sorted<<<flat_grid(nminor + 1, 256), 256, 0, st>>>((int)nminor, s.keys[cur], nnz, nullptr, out_ptr);
+  k_ptr_from_sorted<<<flat_grid(h, nminor + 1, 256), 256, 0, st>>>((int)nminor, s.keys[cur], nnz, nullptr, out_ptr);
   TRY(check_launch(h, "k_ptr_from_sorted"));
   int bad = 0;
   CUDA_TRY(h, cudaMemcpyAsync(&bad, s.flag, sizeof(bad), cudaMemcpyDeviceToHost, st));
@@ -242,7 +242,7 @@ extern "C" int b200sp_csr_to_dense(b200sp_handle_t h, int dtype, int64_t m, int6
   const size_t vs = dtype == B200SP_R_32F ? 4 : 8;
   CUDA_TRY(h, cudaMemsetAsync(dOut, 0, (size_t)m * (size_t)n * vs, h->stream));
   const long long ldr = order == B200SP_ORDER_ROW ? n : 1, ldc = order == B200SP_ORDER_ROW ? 1 : m;
-  const int grid = flat_grid(m, 8);
+  const int grid = flat_grid(h, m, 8);
   if (dtype == B200SP_R_32F)
     k_csr_to_dense<float><<<grid, 256, 0, h->stream>>>((int)m, (int)n, dAp, dAj, (const float *)dAx, (float *)dOut, ldr, ldc);
   else
@@ -263,7 +263,7 @@ extern "C" int b200sp_csr_max_abs_diff(b200sp_handle_t h, int dtype, int64_t m, 
   TRY(ensure(h, h->ws2, 256));
   u64 *res = (u64 *)h->ws2.ptr;
   CUDA_TRY(h, cudaMemsetAsync(res, 0, 2 * sizeof(u64), h->stream));
-  const int grid = flat_grid(m, 8);
+  const int grid = flat_grid(h, m, 8);
   if (dtype == B200SP_R_32F)
     k_csr_max_abs_diff<float><<<grid, 256, 0, h->stream>>>((int)m, dAp, dAj, (const float *)dAx, dBp, dBj, (const float *)dBx, res);
   else

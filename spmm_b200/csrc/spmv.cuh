@@ -64,6 +64,138 @@ k_spmv_vector(int m, const int *__restrict__ Ap, const int *__restrict__ Aj,
   }
 }
 
+// ---- 128-bit variant of the vector kernel -------------------------------------------------------
+// Each lane reads FOUR consecutive (index, value) pairs with one 128-bit load each (fp64 values:
+// two), from the 16-byte aligned position at or below the row start; the entries outside
+// [row begin, row end) are masked.  A group of G lanes therefore covers 4 G entries per trip, so
+// G is a quarter of what the scalar kernel needs (C2, 10.5 entries per row: 4 lanes per row, 8 rows
+// per warp) and the load-instruction count per nonzero drops 4-fold.  Requires Aj / Ax 16-byte
+// aligned (the host checks; allocator blocks are); the last three entries of the arrays are read
+// with scalar loads so that nothing past the end is touched.
+template <typename T> struct Ld4;
+template <> struct Ld4<int> {
+  static __device__ __forceinline__ void ld(const int *p, int (&v)[4]) {
+    const int4 t = __ldcs(reinterpret_cast<const int4 *>(p));
+    v[0] = t.x, v[1] = t.y, v[2] = t.z, v[3] = t.w;
+  }
+};
+template <> struct Ld4<float> {
+  static __device__ __forceinline__ void ld(const float *p, float (&v)[4]) {
+    const float4 t = __ldcs(reinterpret_cast<const float4 *>(p));
+    v[0] = t.x, v[1] = t.y, v[2] = t.z, v[3] = t.w;
+  }
+};
+template <> struct Ld4<double> {
+  static __device__ __forceinline__ void ld(const double *p, double (&v)[4]) {
+    const double2 t = __ldcs(reinterpret_cast<const double2 *>(p)), u = __ldcs(reinterpret_cast<const double2 *>(p + 2));
+    v[0] = t.x, v[1] = t.y, v[2] = u.x, v[3] = u.y;
+  }
+};
+
+template <int G, typename T>
+__global__ void __launch_bounds__(256)
+k_spmv_vector4(int m, int nnz, const int *__restrict__ Ap, const int *__restrict__ Aj,
+               const T *__restrict__ Ax, const T *__restrict__ X, long long ldx, T *__restrict__ Y,
+               long long ldy, T alpha, T beta) {
+  constexpr int R = 4;
+  const int sub = threadIdx.x & (G - 1);
+  const int groups_per_block = 256 / G;
+  const T *x = X + (long long)blockIdx.y * ldx;
+  T *y = Y + (long long)blockIdx.y * ldy;
+  const long long stride = (long long)gridDim.x * groups_per_block;
+  const int vec_end = nnz & ~3;  // entries [0, vec_end) may be read with whole 16-byte loads
+  for (long long row0 = blockIdx.x * groups_per_block + threadIdx.x / G; row0 < m; row0 += stride * R) {
+    int b[R], e[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const long long row = row0 + r * stride;
+      b[r] = e[r] = 0;
+      if (row < m) {
+        b[r] = __ldg(Ap + row);
+        e[r] = __ldg(Ap + row + 1);
+      }
+    }
+    T sum[R];
+    int j[R][4];
+    T a[R][4];
+    int t[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {  // first trip of every row: all loads issued before any is used
+      sum[r] = T(0);
+      t[r] = (b[r] & ~3) + 4 * sub;
+      if (t[r] < e[r]) {
+        if (t[r] < vec_end) {
+          Ld4<int>::ld(Aj + t[r], j[r]);
+          Ld4<T>::ld(Ax + t[r], a[r]);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const bool in = t[r] + c < nnz;
+            j[r][c] = in ? __ldcs(Aj + t[r] + c) : 0;
+            a[r][c] = in ? __ldcs(Ax + t[r] + c) : T(0);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (t[r] < e[r]) {
+        T xv[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int q = t[r] + c;
+          xv[c] = (q >= b[r] && q < e[r]) ? __ldg(x + j[r][c]) : T(0);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int q = t[r] + c;
+          if (q >= b[r] && q < e[r]) sum[r] = fma_acc(a[r][c], xv[c], sum[r]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      for (int tt = t[r] + 4 * G; tt < e[r]; tt += 4 * G) {  // tt >= b: only the row end needs a mask
+        int jj[4];
+        T aa[4];
+        if (tt < vec_end) {
+          Ld4<int>::ld(Aj + tt, jj);
+          Ld4<T>::ld(Ax + tt, aa);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const bool in = tt + c < nnz;
+            jj[c] = in ? __ldcs(Aj + tt + c) : 0;
+            aa[c] = in ? __ldcs(Ax + tt + c) : T(0);
+          }
+        }
+        T xv[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) xv[c] = tt + c < e[r] ? __ldg(x + jj[c]) : T(0);
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (tt + c < e[r]) sum[r] = fma_acc(aa[c], xv[c], sum[r]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+#pragma unroll
+      for (int o = G / 2; o > 0; o >>= 1) sum[r] += __shfl_xor_sync(FULL, sum[r], o, G);
+      const long long row = row0 + r * stride;
+      if (row < m && sub == 0) y[row] = beta == T(0) ? alpha * sum[r] : alpha * sum[r] + beta * y[row];
+    }
+  }
+}
+
+// Longest row of a CSR (decides between the row-group kernel and merge-path; cached per matrix).
+__global__ void __launch_bounds__(256) k_max_row_len(int m, const int *__restrict__ Ap, int *__restrict__ out) {
+  int mx = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
+    mx = max(mx, __ldg(Ap + i + 1) - __ldg(Ap + i));
+  mx = __reduce_max_sync(FULL, mx);
+  if (lane_id() == 0 && mx > 0) atomicMax(out, mx);
+}
+
 // ---- merge-path kernel ------------------------------------------------------------------------
 // The work list is the merge of the m row-end markers with the nnz nonzeros (m + nnz items);
 // every CTA takes SPMV_TILE consecutive items of it, so a tile holds at most SPMV_TILE nonzeros
@@ -115,7 +247,10 @@ __device__ __forceinline__ void spmv_store(T *__restrict__ y, int r, T sum, T al
   y[r] = beta == T(0) ? alpha * sum : alpha * sum + beta * y[r];
 }
 
-template <typename T>
+// VEC: the tile's indices / values are read with 128-bit loads from the first 16-byte aligned entry
+// at or after j0 (two loads of four entries per thread cover the 2048-entry tile); the up to three
+// entries before it are read by the first threads with scalar loads.  Needs Aj / Ax 16-byte aligned.
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(SPMV_THREADS)
 k_spmv_merge(int m, int nnz, const int *__restrict__ tile_row, const int *__restrict__ Ap,
              const int *__restrict__ Aj, const T *__restrict__ Ax, const T *__restrict__ x,
@@ -138,20 +273,64 @@ k_spmv_merge(int m, int nnz, const int *__restrict__ tile_row, const int *__rest
   int jj[SPMV_ITEMS];
   T aa[SPMV_ITEMS];
   int apw[SPMV_ITEMS];
+  int jh = -1;  // VEC: one of the entries in front of the aligned part
+  T ah = T(0);
+  const int vbase = (j0 + 3) & ~3;
+  if (VEC) {
+    const int vec_end = nnz & ~3;
 #pragma unroll
-  for (int q = 0; q < SPMV_ITEMS; ++q) {
-    const int e = q * SPMV_THREADS + tid;
-    jj[q] = e < nz ? __ldcs(Aj + j0 + e) : -1;
-    aa[q] = e < nz ? __ldcs(Ax + j0 + e) : T(0);
-    apw[q] = __ldg(Ap + min(i0 + e, m));
+    for (int q = 0; q < SPMV_ITEMS / 4; ++q) {
+      const int el = vbase + 4 * (q * SPMV_THREADS + tid);
+      int j4[4] = {-1, -1, -1, -1};
+      T a4[4] = {T(0), T(0), T(0), T(0)};
+      if (el < j1) {
+        if (el < vec_end) {
+          Ld4<int>::ld(Aj + el, j4);
+          Ld4<T>::ld(Ax + el, a4);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            if (el + c < j1) {
+              j4[c] = __ldcs(Aj + el + c);
+              a4[c] = __ldcs(Ax + el + c);
+            }
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        jj[q * 4 + c] = el + c < j1 ? j4[c] : -1;
+        aa[q * 4 + c] = a4[c];
+      }
+    }
+    if (j0 + tid < min(vbase, j1)) {
+      jh = __ldcs(Aj + j0 + tid);
+      ah = __ldcs(Ax + j0 + tid);
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < SPMV_ITEMS; ++q) {
+      const int e = q * SPMV_THREADS + tid;
+      jj[q] = e < nz ? __ldcs(Aj + j0 + e) : -1;
+      aa[q] = e < nz ? __ldcs(Ax + j0 + e) : T(0);
+    }
   }
+#pragma unroll
+  for (int q = 0; q < SPMV_ITEMS; ++q) apw[q] = __ldg(Ap + min(i0 + q * SPMV_THREADS + tid, m));
   if (tid < 2) s_ap[SPMV_TILE + tid] = __ldg(Ap + min(i0 + SPMV_TILE + tid, m));
   if (tid == 0) s_nlong = 0;
+  {
+    T xv[SPMV_ITEMS];
 #pragma unroll
-  for (int q = 0; q < SPMV_ITEMS; ++q) {
-    const int e = q * SPMV_THREADS + tid;
-    s_ap[e] = apw[q];
-    if (jj[q] >= 0) s_prod[e] = aa[q] * __ldg(x + jj[q]);
+    for (int q = 0; q < SPMV_ITEMS; ++q) xv[q] = jj[q] >= 0 ? __ldg(x + jj[q]) : T(0);
+    const T xh = jh >= 0 ? __ldg(x + jh) : T(0);
+#pragma unroll
+    for (int q = 0; q < SPMV_ITEMS; ++q) {
+      s_ap[q * SPMV_THREADS + tid] = apw[q];
+      // tile-relative position of the entry held in slot q
+      const int e = VEC ? (vbase - j0) + 4 * ((q >> 2) * SPMV_THREADS + tid) + (q & 3) : q * SPMV_THREADS + tid;
+      if (jj[q] >= 0) s_prod[e] = aa[q] * xv[q];
+    }
+    if (jh >= 0) s_prod[tid] = ah * xh;
   }
   __syncthreads();
   // rows: s_ap[t] = Ap[i0 + t].  Row i0 may have begun in an earlier tile (head); row i1 is the

@@ -44,6 +44,55 @@ def _scalar(value, np_dtype):
     return buf, buf.ctypes.data_as(ctypes.c_void_p)
 
 
+class SpgemmPlan:
+    """The two halves of `spgemm` apart: the structure pass has run (C.indptr and nnz(C) are
+    known, the one host synchronisation of cusparse.py:2120-2127 is behind us), the value pass is
+    `numeric()`.  The row-panel driver (multi.py) plans all its panels first, learns where each
+    lands in the shared host buffer, then runs the value passes.  `handle=None` uses the calling
+    thread's handle, which keeps ONE plan: pass a private handle (`_lib.new_handle`) to keep
+    several plans alive."""
+
+    def __init__(self, a, b, alg=0, chunk_fraction=0.2, handle=None):
+        m, k = a.shape
+        _, n = b.shape
+        self.a, self.b = _cast_common_type(a, b)
+        self.shape = (m, n)
+        self.dtype = self.a.dtype
+        dev = self.device = self.a.device
+        lib = _lib.load()
+        self.h = handle if handle is not None else _lib.handle(dev.index)
+        _bind_stream(self.h, dev)
+        self.indptr = torch.empty(m + 1, dtype=torch.int32, device=dev)  # cusparse.py:2039
+        prods, c_nnz = ctypes.c_int64(0), ctypes.c_int64(0)
+        _lib.check(self.h, lib.b200sp_spgemm_symbolic(
+            self.h, m, k, n, self.a.nnz, self.b.nnz, self.a.indptr.data_ptr(), self.a.indices.data_ptr(),
+            self.b.indptr.data_ptr(), self.b.indices.data_ptr(), int(alg), float(chunk_fraction),
+            ctypes.byref(prods), ctypes.byref(c_nnz), self.indptr.data_ptr()))
+        self.nnz = int(c_nnz.value)
+        self.num_products = int(prods.value)
+
+    def numeric(self, alpha=1, out=None):
+        """Fill C.indices / C.data (allocated here from torch's allocator unless `out` =
+        (indices, data) tensors with room for nnz entries is given) and return the csr_matrix."""
+        dev, dt, nnz = self.device, self.dtype, self.nnz
+        _bind_stream(self.h, dev)
+        if out is None:
+            try:
+                c_indices = torch.empty(nnz, dtype=torch.int32, device=dev)  # cusparse.py:2128-2129
+                c_data = torch.empty(nnz, dtype=_TORCH_DT[dt], device=dev)
+            except torch.OutOfMemoryError as e:  # same except clause as the reference's callers
+                raise MemoryError(str(e)) from e
+        else:
+            c_indices, c_data = out[0][:nnz], out[1][:nnz]
+        _abuf, aptr = _scalar(alpha, dt)
+        _lib.check(self.h, _lib.load().b200sp_spgemm_numeric(
+            self.h, _dt_code(dt), aptr, self.a.data.data_ptr(), self.b.data.data_ptr(), c_indices.data_ptr(),
+            c_data.data_ptr()))
+        c = csr_matrix((c_data, c_indices, self.indptr), shape=self.shape)
+        c._canonical = True
+        return c
+
+
 def spgemm(a, b, alpha=1, alg=0, chunk_fraction=0.2, verbose=False):
     """C = alpha * A * B for CSR matrices (reference: cusparse.py:2007-2142).
 
@@ -63,42 +112,17 @@ def spgemm(a, b, alpha=1, alg=0, chunk_fraction=0.2, verbose=False):
     assert b.has_canonical_format
     if a.shape[1] != b.shape[0]:
         raise ValueError("mismatched shape")
-    m, k = a.shape
-    _, n = b.shape
-    a, b = _cast_common_type(a, b)
-    dt = a.dtype
-    dev = a.device
-    lib = _lib.load()
-    h = _lib.handle(dev.index)
-    _bind_stream(h, dev)
     if alg not in (2, 3):
         alg = 0
     elif not (0.0 < float(chunk_fraction) <= 1.0):
         raise ValueError(f"chunk_fraction must be in (0,1], got {chunk_fraction}")
     elif verbose:
         print("USING ALG3 or ALG2")
-    c_indptr = torch.empty(m + 1, dtype=torch.int32, device=dev)  # cusparse.py:2039
-    prods = ctypes.c_int64(0)
-    c_nnz = ctypes.c_int64(0)
-    _lib.check(h, lib.b200sp_spgemm_symbolic(
-        h, m, k, n, a.nnz, b.nnz, a.indptr.data_ptr(), a.indices.data_ptr(), b.indptr.data_ptr(),
-        b.indices.data_ptr(), int(alg), float(chunk_fraction), ctypes.byref(prods), ctypes.byref(c_nnz),
-        c_indptr.data_ptr()))
-    nnz = int(c_nnz.value)
+    plan = SpgemmPlan(a, b, alg=alg, chunk_fraction=chunk_fraction)
     if verbose:
-        s = _lib.stats(dev.index)
-        print("workspace GB =", s.workspace_bytes / (1024 ** 3), "products =", prods.value)
-    try:
-        c_indices = torch.empty(nnz, dtype=torch.int32, device=dev)  # cusparse.py:2128-2129
-        c_data = torch.empty(nnz, dtype=_TORCH_DT[dt], device=dev)
-    except torch.OutOfMemoryError as e:  # same except clause as the reference's callers
-        raise MemoryError(str(e)) from e
-    _abuf, aptr = _scalar(alpha, dt)
-    _lib.check(h, lib.b200sp_spgemm_numeric(h, _dt_code(dt), aptr, a.data.data_ptr(), b.data.data_ptr(),
-                                            c_indices.data_ptr(), c_data.data_ptr()))
-    c = csr_matrix((c_data, c_indices, c_indptr), shape=(m, n))
-    c._canonical = True
-    return c
+        s = _lib.stats(plan.device.index)
+        print("workspace GB =", s.workspace_bytes / (1024 ** 3), "products =", plan.num_products)
+    return plan.numeric(alpha)
 
 
 def spmv(a, x, y=None, alpha=1, beta=0, transa=False):

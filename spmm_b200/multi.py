@@ -1,10 +1,28 @@
-"""Row-panel multi-GPU SpGEMM: one process per GPU (torch.distributed), A split into
-contiguous row panels balanced by intermediate products, B broadcast once over NCCL/NVLink,
-C row panels concatenated on the host (BASELINE.json north_star).
+"""Row-panel multi-GPU SpGEMM / SpMV: one process per GPU (torch.distributed), A split into row
+panels balanced by intermediate products, B broadcast once over NCCL/NVLink, C row panels landed
+in ONE host buffer shared by all ranks (BASELINE.json north_star).
 
 The reference has no multi-GPU path; Gustavson rows are independent, so the only exchange
-step is the broadcast of B (one packed buffer: indptr | indices | data).  No reduction.
+step is the broadcast of B (one packed buffer: indptr | indices | data - the message shape of
+the reference's vendored `_SparseNCCLCommunicator.broadcast`, cupyx/distributed/_nccl_comm.py:651-673,
+metadata first, then the arrays).  No reduction.
+
+Flow of `spgemm_row_panels` (every rank):
+  1. B (rank 0) is cast to int32 / fp32|fp64, uploaded and broadcast (one `dist.broadcast`);
+  2. the rows of A are cut into world * panels_per_rank product-balanced panels dealt round-robin
+     (`block_cyclic_panels`), each cut again where its output could exceed the int32 CSR limit;
+  3. structure pass of every sub-panel (`cusparse.SpgemmPlan`, one private library handle each);
+  4. one all-gather of the per-sub-panel nnz(C): every rank now knows, by an exclusive scan in row
+     order, where each of its sub-panels starts in the concatenated C;
+  5. value pass per sub-panel into one of two device buffers, D2H on a second stream straight to
+     that offset of the shared host buffer (POSIX shared memory mapped and page-locked by every
+     rank) while the next sub-panel computes; the rebased indptr slice is written next to it;
+  6. barrier; rank 0 holds the whole C as views of the shared buffer.
 """
+import atexit
+import mmap
+import os
+
 import numpy as np
 
 try:  # torch is plumbing only; the partition helpers below work without it
@@ -13,6 +31,8 @@ try:  # torch is plumbing only; the partition helpers below work without it
 except Exception:  # pragma: no cover
     torch = None
     dist = None
+
+INT32_MAX = (1 << 31) - 1
 
 
 # ------------------------------------------------------------------ partition (host) ----
@@ -27,18 +47,28 @@ def row_products(Ap, Aj, Bp):
 
 
 def balanced_row_panels(weights, nparts):
-    """Contiguous panels [b[r], b[r+1]) with near-equal total weight (prefix-sum split).
+    """Contiguous panels [b[r], b[r+1]) with near-equal total weight.  Greedy with re-targeting:
+    panel r ends where the running weight is closest to an equal share of what is LEFT, and takes
+    at least one row while rows remain - so a dominant first row (an R-MAT hub) ends its own panel
+    and the other parts still share the rest, instead of every boundary collapsing onto it.
     Returns nparts+1 boundaries; panels may be empty when there are fewer rows than parts."""
     w = np.asarray(weights, dtype=np.int64) + 1  # +1: rows without products still cost a visit
     csum = np.cumsum(w)
-    total = int(csum[-1]) if len(csum) else 0
-    bounds = [0]
-    for r in range(1, nparts):
-        target = total * r / nparts
-        bounds.append(int(np.searchsorted(csum, target, side="left")))
-    bounds.append(len(w))
-    for r in range(1, len(bounds)):
-        bounds[r] = max(bounds[r], bounds[r - 1])
+    nrows = len(w)
+    total = int(csum[-1]) if nrows else 0
+    bounds, start, base = [0], 0, 0
+    for r in range(nparts - 1):
+        target = base + (total - base) / (nparts - r)
+        i = int(np.searchsorted(csum, target, side="left"))  # csum[i] is the first prefix >= target
+        end = i
+        if i < nrows:
+            below = float(csum[i - 1]) if i > 0 else 0.0
+            if float(csum[i]) - target <= target - below:
+                end = i + 1
+        end = min(max(end, start + 1), nrows)
+        bounds.append(end)
+        start, base = end, (int(csum[end - 1]) if end > 0 else 0)
+    bounds.append(nrows)
     return bounds
 
 
@@ -70,12 +100,12 @@ def concat_panels(panels):
         ptrs.append(np.asarray(p[1:], dtype=np.int64) + off)
         off += int(p[-1])
     ptr = np.concatenate(ptrs)
-    if off <= np.iinfo(np.int32).max:
+    if off <= INT32_MAX:
         ptr = ptr.astype(np.int32)
     return (ptr, np.concatenate([j for _, j, _ in panels]), np.concatenate([x for _, _, x in panels]))
 
 
-def split_rows_by_bound(row_prods, n_cols, r0, r1, limit=(1 << 31) - 1):
+def split_rows_by_bound(row_prods, n_cols, r0, r1, limit=INT32_MAX):
     """Cut rows [r0, r1) into consecutive sub-panels whose nnz(C) cannot exceed `limit`:
     nnz(C_i) <= min(products_i, n_cols), so the running sum of that bound decides the cuts.
     Returns the list of boundaries [r0, ..., r1].  A single row always fits (bound <= n_cols)."""
@@ -92,7 +122,20 @@ def split_rows_by_bound(row_prods, n_cols, r0, r1, limit=(1 << 31) - 1):
     return bounds
 
 
-def spgemm_panels(A, b_dev, shape, r0=0, r1=None, limit=(1 << 31) - 1, alg=0, chunk_fraction=0.2, alpha=1.0,
+def plan_sub_panels(row_prods, n_cols, world, per_part=4, limit=INT32_MAX):
+    """The whole decomposition, identical on every rank: list over ranks of that rank's
+    sub-panels [(p0, p1), ...] in ascending row order."""
+    out = []
+    for ranges in block_cyclic_panels(row_prods, world, per_part):
+        subs = []
+        for r0, r1 in ranges:
+            cuts = split_rows_by_bound(row_prods, n_cols, r0, r1, limit)
+            subs.extend(zip(cuts[:-1], cuts[1:]))
+        out.append(subs)
+    return out
+
+
+def spgemm_panels(A, b_dev, shape, r0=0, r1=None, limit=INT32_MAX, alg=0, chunk_fraction=0.2, alpha=1.0,
                   row_prods=None):
     """Generator over the C sub-panels of rows [r0, r1) of A @ B on the current GPU.
 
@@ -117,8 +160,27 @@ def spgemm_panels(A, b_dev, shape, r0=0, r1=None, limit=(1 << 31) - 1, alg=0, ch
 
 # ------------------------------------------------------------------- B broadcast ----------
 
+def cast_csr_host(M, val_dtype=None):
+    """(indptr, indices, data) as C-contiguous int32 / int32 / fp32|fp64 host arrays.  SciPy hands
+    out int64 index arrays for large or COO-built matrices; the packed broadcast below is sized
+    for int32, so everything is cast here and an index that does not fit raises."""
+    p, j, x = (M.indptr, M.indices, M.data) if hasattr(M, "indptr") else M
+    p, j, x = np.asarray(p), np.asarray(j), np.asarray(x)
+    if len(p) and int(p[-1]) > INT32_MAX:
+        raise OverflowError("nnz does not fit the int32 indptr of CSR")
+    if j.size and j.dtype.itemsize > 4 and (int(j.max()) > INT32_MAX or int(j.min()) < 0):
+        raise OverflowError("a column index does not fit int32")
+    vdt = np.dtype(val_dtype) if val_dtype is not None else (np.dtype(np.float64) if x.dtype == np.float64 else np.dtype(np.float32))
+    if vdt not in (np.float32, np.float64):
+        raise ValueError(f"Only float32 and float64 are supported (got {vdt})")
+    return (np.ascontiguousarray(p, dtype=np.int32), np.ascontiguousarray(j, dtype=np.int32),
+            np.ascontiguousarray(x, dtype=vdt))
+
+
 def pack_csr(p, j, x):
     """One contiguous byte buffer: indptr | indices | data (single collective, one launch)."""
+    if p.dtype != torch.int32 or j.dtype != torch.int32 or x.dtype not in (torch.float32, torch.float64):
+        raise TypeError("pack_csr expects int32 indptr / indices and float32 / float64 values")
     return torch.cat([p.contiguous().view(torch.uint8), j.contiguous().view(torch.uint8),
                       x.contiguous().view(torch.uint8)])
 
@@ -130,8 +192,9 @@ def unpack_csr(buf, nrows, nnz, val_dtype):
 
 
 def broadcast_csr(B, src=0, device=None):
-    """Broadcast a CSR (tuple of tensors on `src`, None elsewhere).  Metadata (rows, nnz, dtype
-    code) goes first as 3 int64, then the packed arrays in one dist.broadcast."""
+    """Broadcast a CSR (tuple of int32 / int32 / fp32|fp64 tensors on `src`, None elsewhere).
+    Metadata (rows, nnz, dtype code) goes first as 3 int64, then the packed arrays in one
+    dist.broadcast."""
     rank = dist.get_rank()
     device = device or (B[0].device if B is not None else torch.device("cpu"))
     meta = torch.zeros(3, dtype=torch.int64, device=device)
@@ -142,70 +205,273 @@ def broadcast_csr(B, src=0, device=None):
     nrows, nnz, code = (int(v) for v in meta.tolist())
     vdt = torch.float64 if code else torch.float32
     nbytes = (nrows + 1) * 4 + nnz * 4 + nnz * (8 if code else 4)
-    buf = pack_csr(*B) if rank == src else torch.empty(nbytes, dtype=torch.uint8, device=device)
+    if rank == src:
+        buf = pack_csr(*B)
+        if buf.numel() != nbytes:
+            raise ValueError(f"packed CSR has {buf.numel()} bytes, metadata says {nbytes}")
+    else:
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
     dist.broadcast(buf, src=src)
     return unpack_csr(buf, nrows, nnz, vdt)
 
 
+# ------------------------------------------------------- the shared host buffer of C ------
+
+class HostArena:
+    """One host buffer mapped by every rank of the job: a file in /dev/shm (tmpfs) created by
+    rank 0, mmap'ed by all, and - on the CUDA path - page-locked in every process with
+    b200sp_host_register, so that each rank's D2H copies land at its offset at DMA speed and the
+    concatenation costs nothing.  Grow-only and cached across calls (page-locking gigabytes takes
+    longer than the product itself)."""
+
+    def __init__(self):
+        self.path, self.mm, self.size, self.base, self.registered, self.owner = None, None, 0, None, False, False
+
+    def _close(self):
+        if self.mm is None:
+            return
+        if self.registered:
+            from . import _lib
+            _lib.load().b200sp_host_unregister(self.base.ctypes.data)
+        self.base = None
+        try:
+            self.mm.close()
+        except BufferError:  # views handed to the caller are still alive; the mapping goes with them
+            pass
+        if self.owner and self.path and os.path.exists(self.path):
+            os.unlink(self.path)
+        self.mm, self.size, self.registered = None, 0, False
+
+    def ensure(self, nbytes, rank, register):
+        """Collective: all ranks call with the same nbytes."""
+        if nbytes <= self.size:
+            return
+        self._close()
+        size = max(4096, (int(nbytes * 1.25) + 4095) & ~4095)
+        name = [None]
+        if rank == 0:
+            root = "/dev/shm" if os.path.isdir("/dev/shm") else (os.environ.get("TMPDIR") or "/tmp")
+            name[0] = os.path.join(root, f"b200sp_c_{os.getpid()}_{np.random.default_rng().integers(1 << 30)}")
+            fd = os.open(name[0], os.O_CREAT | os.O_RDWR | os.O_EXCL, 0o600)
+            os.ftruncate(fd, size)
+            os.close(fd)
+        dist.broadcast_object_list(name, src=0)
+        self.path, self.owner = name[0], rank == 0
+        fd = os.open(self.path, os.O_RDWR)
+        try:
+            self.mm = mmap.mmap(fd, size)
+        finally:
+            os.close(fd)
+        self.size = size
+        self.base = np.frombuffer(self.mm, dtype=np.uint8)
+        if register:
+            from . import _lib
+            st = _lib.load().b200sp_host_register(self.base.ctypes.data, size)
+            if st != _lib.OK:
+                raise MemoryError(f"cudaHostRegister of the shared C buffer ({size} bytes) failed")
+            self.registered = True
+        dist.barrier()  # everyone has the file open: rank 0 may drop the name
+        if self.owner:
+            os.unlink(self.path)
+
+    def view(self, offset, count, dtype):
+        return np.frombuffer(self.mm, dtype=dtype, count=count, offset=offset)
+
+
+_ARENA = HostArena() if torch is not None else None
+if _ARENA is not None:
+    atexit.register(_ARENA._close)
+
+
+def _layout(m, nnz, vsize):
+    """Offsets of [indptr int64 (m+1) | indices int32 nnz | data nnz*vsize] in the arena."""
+    o_j = ((m + 1) * 8 + 4095) & ~4095
+    o_x = (o_j + nnz * 4 + 4095) & ~4095
+    return o_j, o_x, o_x + nnz * vsize
+
+
 # ------------------------------------------------------------------- driver ----------------
 
-def spgemm_row_panels(A, B, shape, alg=0, chunk_fraction=0.2, alpha=1.0, compute=None, gather=True):
+class _InjectedEngine:
+    """Sub-panel engine around a caller-supplied `compute` (host-logic tests on gloo / CPU)."""
+
+    def __init__(self, compute, Bd, k, n, dev):
+        self.compute, self.Bd, self.k, self.n, self.dev, self.res = compute, Bd, k, n, dev, []
+
+    def plan(self, panel):
+        t = tuple(torch.from_numpy(np.ascontiguousarray(a)).to(self.dev) for a in panel)
+        cp, cj, cx = self.compute(t, self.Bd, (len(panel[0]) - 1, self.k, self.n))
+        self.res.append((cp.cpu().numpy(), cj.cpu().numpy(), cx.cpu().numpy()))
+        return int(self.res[-1][0][-1])
+
+    def finish(self, i, dst_j, dst_x):
+        cp, cj, cx = self.res[i]
+        dst_j[:] = cj
+        dst_x[:] = cx
+        return cp
+
+    def close(self):
+        self.res = []
+
+
+class _GpuEngine:
+    """Sub-panel engine on libb200sp: structure pass per sub-panel now (private handle, the plan
+    stays alive), value pass + D2H later, double-buffered so the copy of sub-panel i runs under
+    the kernels of sub-panel i + 1."""
+
+    def __init__(self, Bd, k, n, dev, alg, chunk_fraction, alpha):
+        from .sparse import csr_matrix
+        self.dev, self.k, self.n, self.alg, self.cf, self.alpha = dev, k, n, alg, chunk_fraction, alpha
+        self.b = csr_matrix((Bd[2], Bd[1], Bd[0]), shape=(k, n))
+        self.b._canonical = True
+        self.plans, self.handles, self.keep = [], [], []
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.bufs, self.buf_free = None, None
+
+    def plan(self, panel):
+        from . import _lib, cusparse
+        from .sparse import csr_matrix
+        pp, pj, px = panel
+        a = csr_matrix((np.ascontiguousarray(px), np.ascontiguousarray(pj), pp), shape=(len(pp) - 1, self.k))
+        a._canonical = True
+        h = _lib.new_handle(self.dev.index)
+        self.handles.append(h)
+        p = cusparse.SpgemmPlan(a, self.b, alg=self.alg, chunk_fraction=self.cf, handle=h)
+        self.plans.append(p)
+        return p.nnz
+
+    def finish(self, i, dst_j, dst_x):
+        from . import _lib
+        p = self.plans[i]
+        if self.bufs is None:  # two (indices, data) device buffers of the largest sub-panel
+            cap = max(1, max(q.nnz for q in self.plans))
+            vdt = self.b.data.dtype
+            self.bufs = [(torch.empty(cap, dtype=torch.int32, device=self.dev), torch.empty(cap, dtype=vdt, device=self.dev))
+                         for _ in range(2)]
+            self.buf_free = [None, None]
+        slot = i & 1
+        cur = torch.cuda.current_stream(self.dev)
+        if self.buf_free[slot] is not None:
+            cur.wait_event(self.buf_free[slot])  # the D2H of sub-panel i - 2 has left this buffer
+        c = p.numeric(self.alpha, out=self.bufs[slot])
+        done = torch.cuda.Event()
+        done.record(cur)
+        self.copy_stream.wait_event(done)
+        lib, h = _lib.load(), self.handles[i]
+        sp = self.copy_stream.cuda_stream
+        if p.nnz:
+            _lib.check(h, lib.b200sp_memcpy_async(h, dst_j.ctypes.data, c.indices.data_ptr(), p.nnz * 4, 1, sp))
+            _lib.check(h, lib.b200sp_memcpy_async(h, dst_x.ctypes.data, c.data.data_ptr(), p.nnz * dst_x.itemsize, 1, sp))
+        ev = torch.cuda.Event()
+        ev.record(self.copy_stream)
+        self.buf_free[slot] = ev
+        cp = p.indptr.cpu().numpy()  # small; also orders the host behind this sub-panel's kernels
+        self.plans[i] = None
+        return cp
+
+    def close(self):
+        from . import _lib
+        self.copy_stream.synchronize()
+        torch.cuda.current_stream(self.dev).synchronize()
+        for h in self.handles:
+            _lib.destroy_handle(h)
+        self.handles, self.plans, self.bufs = [], [], None
+
+
+def spgemm_row_panels(A, B, shape, alg=0, chunk_fraction=0.2, alpha=1.0, compute=None, gather=True,
+                      panels_per_rank=4, limit=INT32_MAX, copy=False, stats=None):
     """C = alpha * A @ B over all ranks of the default process group.
 
-    A: host CSR triple (numpy), present on every rank (each rank uploads only its panel);
-    B: host CSR triple on rank 0 (None elsewhere) - it is uploaded once and broadcast.
-    compute(panel_triple_on_device, B_triple_on_device, (mp, k, n)) -> device C triple; the
-    default is the libb200sp GPU path (tests of the host logic may inject another).
-    Returns the concatenated host C on rank 0 when gather=True (None elsewhere), else this
-    rank's (r0, r1, host C panel).
+    A: host CSR triple (numpy), present on every rank (each rank uploads only its panels);
+    B: host CSR (scipy matrix or triple) on rank 0 (None elsewhere) - uploaded once and broadcast.
+    compute(panel_triple_on_device, B_triple_on_device, (mp, k, n)) -> C triple: tests of the host
+    logic may inject one; the default is the libb200sp GPU path.
+    gather=True: returns (indptr, indices, data) of the whole C on rank 0 (None elsewhere) - views
+    of the shared host buffer, valid until the next call (copy=True: private copies); indptr is
+    int32 when nnz(C) fits, int64 otherwise.
+    gather=False: returns this rank's [(p0, p1, (indptr, indices, data)), ...] sub-panels (views).
+    stats: optional dict that receives sub-panel counts / nnz.
     """
     rank, world = dist.get_rank(), dist.get_world_size()
-    m, k, n = shape
-    Ap, Aj, Ax = A
+    m, k, n = (int(v) for v in shape)
     backend = dist.get_backend()
-    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+    on_gpu = backend == "nccl"
+    dev = torch.device("cuda", torch.cuda.current_device()) if on_gpu else torch.device("cpu")
+    Ap, Aj, Ax = A
     Bd = None
     if rank == 0:
-        Bd = tuple(torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in B)
+        Bd = tuple(torch.from_numpy(a).to(dev) for a in cast_csr_host(B))
     Bd = broadcast_csr(Bd, src=0, device=dev)
+    vnp = np.dtype(np.float64) if Bd[2].dtype == torch.float64 else np.dtype(np.float32)
     Bp_host = Bd[0].cpu().numpy()
-    bounds = balanced_row_panels(row_products(Ap, Aj, Bp_host), world)
-    r0, r1 = bounds[rank], bounds[rank + 1]
-    pp, pj, px = slice_rows(Ap, Aj, Ax, r0, r1)
-    panel = tuple(torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (pp, pj, px))
+    row_prods = row_products(Ap, Aj, Bp_host)
+    subs_all = plan_sub_panels(row_prods, n, world, panels_per_rank, limit)
+    mine = subs_all[rank]
     if compute is None:
-        compute = _gpu_compute(alg, chunk_fraction, alpha)
-    cp, cj, cx = compute(panel, Bd, (r1 - r0, k, n))
-    host_c = (cp.cpu().numpy(), cj.cpu().numpy(), cx.cpu().numpy())
+        if not on_gpu:
+            raise RuntimeError("spgemm_row_panels needs the NCCL backend (one GPU per rank); there is no CPU fallback")
+        eng = _GpuEngine(Bd, k, n, dev, alg, chunk_fraction, alpha)
+    else:
+        eng = _InjectedEngine(compute, Bd, k, n, dev)
+    try:
+        # ---- structure pass of every sub-panel, then one exchange of the counts ------------
+        Ajc, Axc = np.asarray(Aj), np.asarray(Ax, dtype=vnp)  # one cast, the sub-panels are views
+        if Ajc.dtype != np.int32:
+            Ajc = Ajc.astype(np.int32)
+        my_nnz = [eng.plan(slice_rows(Ap, Ajc, Axc, p0, p1)) for p0, p1 in mine]
+        width = max(1, max(len(s) for s in subs_all))
+        mine_t = torch.zeros(width, dtype=torch.int64, device=dev)
+        if my_nnz:
+            mine_t[:len(my_nnz)] = torch.tensor(my_nnz, dtype=torch.int64)
+        allc = [torch.zeros(width, dtype=torch.int64, device=dev) for _ in range(world)]
+        dist.all_gather(allc, mine_t)
+        counts = [t.cpu().numpy() for t in allc]
+        # exclusive scan over all sub-panels in row order
+        order = sorted((p0, r, i) for r, subs in enumerate(subs_all) for i, (p0, _p1) in enumerate(subs))
+        offsets, run = {}, 0
+        for _p0, r, i in order:
+            offsets[(r, i)] = run
+            run += int(counts[r][i])
+        total = run
+        o_j, o_x, nbytes = _layout(m, total, vnp.itemsize)
+        _ARENA.ensure(nbytes, rank, register=on_gpu and compute is None)
+        ptr = _ARENA.view(0, m + 1, np.int64)
+        idx = _ARENA.view(o_j, total, np.int32)
+        val = _ARENA.view(o_x, total, vnp)
+        if rank == 0:
+            ptr[0] = 0
+        # ---- value pass + D2H to the sub-panel's offset ------------------------------------
+        for i, (p0, p1) in enumerate(mine):
+            off, cnt = offsets[(rank, i)], int(my_nnz[i])
+            cp = eng.finish(i, idx[off:off + cnt], val[off:off + cnt])
+            ptr[p0 + 1:p1 + 1] = cp[1:].astype(np.int64) + off
+    finally:
+        eng.close()
+    if stats is not None:
+        stats.update({"sub_panels": [len(s) for s in subs_all], "nnz": total, "my_nnz": int(sum(my_nnz))})
+    dist.barrier()  # all panels are in the buffer
     if not gather:
-        return r0, r1, host_c
-    out = [None] * world if rank == 0 else None
-    dist.gather_object(host_c, out, dst=0)
-    return concat_panels(out) if rank == 0 else None
-
-
-def _gpu_compute(alg, chunk_fraction, alpha):
-    from . import cusparse
-    from .sparse import csr_matrix
-
-    def run(panel, Bd, shape):
-        mp, k, n = shape
-        a = csr_matrix((panel[2], panel[1], panel[0]), shape=(mp, k))
-        b = csr_matrix((Bd[2], Bd[1], Bd[0]), shape=(k, n))
-        a._canonical = b._canonical = True
-        c = cusparse.spgemm(a, b, alpha=alpha, alg=alg, chunk_fraction=chunk_fraction)
-        return c.indptr, c.indices, c.data
-    return run
+        out = []
+        for i, (p0, p1) in enumerate(mine):
+            off, cnt = offsets[(rank, i)], int(my_nnz[i])
+            lp = (ptr[p0:p1 + 1] - off).astype(np.int32)
+            lp[0] = 0
+            out.append((p0, p1, (lp, idx[off:off + cnt], val[off:off + cnt])))
+        return out
+    if rank != 0:
+        return None
+    res = (ptr.astype(np.int32) if total <= INT32_MAX else ptr, idx, val)
+    return tuple(np.array(a) for a in res) if copy else res
 
 
 def spmv_row_panels(A, x, shape, compute=None, gather=True):
     """y = A @ x over all ranks: contiguous row panels of A balanced by nonzeros, x broadcast
-    from rank 0 (one dist.broadcast), no reduction; y panels concatenated on rank 0
-    (SURVEY.md section 8e).
+    from rank 0 (one dist.broadcast), no reduction; y panels all-gathered (padded to the longest
+    panel: one collective on the device) and concatenated.
 
     A: host CSR triple on every rank; x: host vector on rank 0 (None elsewhere).
     compute(panel_triple_on_device, x_on_device, (mp, n)) -> device y panel; default = the GPU path.
-    Returns y (numpy, length m) on rank 0 when gather=True (None elsewhere), else (r0, r1, y panel).
+    Returns y (numpy, length m) on every rank when gather=True, else (r0, r1, y panel).
     """
     rank, world = dist.get_rank(), dist.get_world_size()
     m, n = shape
@@ -224,12 +490,15 @@ def spmv_row_panels(A, x, shape, compute=None, gather=True):
     panel = tuple(torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (pp, pj, px))
     if compute is None:
         compute = _gpu_spmv
-    y = compute(panel, xd, (r1 - r0, n)).cpu().numpy()
+    y = compute(panel, xd, (r1 - r0, n))
     if not gather:
-        return r0, r1, y
-    out = [None] * world if rank == 0 else None
-    dist.gather_object(y, out, dst=0)
-    return np.concatenate(out) if rank == 0 else None
+        return r0, r1, y.cpu().numpy()
+    width = max(1, max(bounds[r + 1] - bounds[r] for r in range(world)))
+    mine = torch.zeros(width, dtype=vdt, device=dev)
+    mine[:r1 - r0] = y.to(vdt).reshape(-1)
+    parts = [torch.empty(width, dtype=vdt, device=dev) for _ in range(world)]
+    dist.all_gather(parts, mine)
+    return torch.cat([parts[r][:bounds[r + 1] - bounds[r]] for r in range(world)]).cpu().numpy()
 
 
 def _gpu_spmv(panel, xd, shape):

@@ -31,6 +31,38 @@ def test_row_products_and_balanced_panels():
     # more parts than rows: empty panels are legal
     b = multi.balanced_row_panels(np.array([5, 5]), 4)
     assert b[0] == 0 and b[-1] == 2 and len(b) == 5
+    # a dominant first row (an R-MAT hub) ends its own panel; the other ranks still get rows
+    b = multi.balanced_row_panels(np.array([100, 0, 0, 0, 0, 0, 0, 1]), 4)
+    assert b[0] == 0 and b[1] == 1 and b[-1] == 8
+    b = multi.balanced_row_panels(np.array([1000, 10, 10, 10, 10, 10, 10, 10, 10]), 2)
+    assert b == [0, 1, 9]
+
+
+def test_cast_csr_host_int64_indices():
+    """SciPy hands out int64 index arrays for COO-built matrices: the packed broadcast is sized
+    for int32, so the host cast must normalise them (and refuse what does not fit)."""
+    M = helpers.random_csr(12, 9, 0.4, 5, dtype=np.float64)
+    p, j, x = multi.cast_csr_host((M.indptr.astype(np.int64), M.indices.astype(np.int64), M.data.astype(np.float64)))
+    assert p.dtype == np.int32 and j.dtype == np.int32 and x.dtype == np.float64
+    assert np.array_equal(p, M.indptr) and np.array_equal(j, M.indices)
+    assert multi.cast_csr_host(M, np.float32)[2].dtype == np.float32
+    with pytest.raises(OverflowError):
+        multi.cast_csr_host((np.array([0, 1], np.int64), np.array([1 << 31], np.int64), np.ones(1, np.float32)))
+    with pytest.raises(TypeError):
+        multi.pack_csr(torch.zeros(2, dtype=torch.int64), torch.zeros(1, dtype=torch.int32), torch.zeros(1))
+
+
+def test_plan_sub_panels_cover_rows_once():
+    rng = np.random.default_rng(6)
+    rp = (rng.pareto(1.1, size=500) * 40).astype(np.int64)
+    for world, per, limit in ((1, 1, 10 ** 9), (2, 4, 10 ** 9), (4, 4, 300), (3, 2, 50)):
+        subs = multi.plan_sub_panels(rp, 64, world, per, limit)
+        assert len(subs) == world
+        flat = sorted(s for part in subs for s in part)
+        assert flat[0][0] == 0 and flat[-1][1] == len(rp)
+        assert all(flat[i][1] == flat[i + 1][0] for i in range(len(flat) - 1))
+        ub = np.minimum(rp, 64)
+        assert all(ub[a:b].sum() <= limit or b - a == 1 for a, b in flat)
 
 
 def test_block_cyclic_panels_cover_rows_once():
@@ -88,12 +120,16 @@ def _worker(rank, world, port, q):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         A, B = helpers.skewed_pair(k=4500, n=9000)
-        Bt = helpers.triple(B) if rank == 0 else None          # only rank 0 holds B
-        out = multi.spgemm_row_panels(helpers.triple(A), Bt, (A.shape[0], A.shape[1], B.shape[1]),
-                                      compute=_oracle_compute)
-        r0, r1, panel = multi.spgemm_row_panels(helpers.triple(A), Bt, (A.shape[0], A.shape[1], B.shape[1]),
-                                                compute=_oracle_compute, gather=False)
-        q.put((rank, out, (r0, r1, panel[0][-1])))
+        # only rank 0 holds B, and with int64 index arrays (what scipy builds from COO input)
+        Bt = (B.indptr.astype(np.int64), B.indices.astype(np.int64), B.data) if rank == 0 else None
+        shape = (A.shape[0], A.shape[1], B.shape[1])
+        st = {}
+        out = multi.spgemm_row_panels(helpers.triple(A), Bt, shape, compute=_oracle_compute, copy=True, stats=st)
+        # a small limit forces extra sub-panel cuts; the shared buffer is reused (no growth)
+        subs = multi.spgemm_row_panels(helpers.triple(A), Bt, shape, compute=_oracle_compute, gather=False,
+                                       panels_per_rank=3, limit=40000)
+        info = [(p0, p1, int(c[0][-1]), int(c[1].size), c[0].dtype == np.int32 and int(c[0][0]) == 0) for p0, p1, c in subs]
+        q.put((rank, out, info, st))
     finally:
         dist.destroy_process_group()
 
@@ -108,8 +144,8 @@ def test_row_panels_world2_gloo():
         p.start()
     res = {}
     for _ in range(2):
-        rank, out, info = q.get(timeout=90)
-        res[rank] = (out, info)
+        rank, out, info, st = q.get(timeout=90)
+        res[rank] = (out, info, st)
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
@@ -117,10 +153,17 @@ def test_row_panels_world2_gloo():
     A, B = helpers.skewed_pair(k=4500, n=9000)
     C = (A @ B).tocsr()
     C.sort_indices()
-    helpers.assert_csr_bitwise(res[0][0], helpers.triple(C), "world2 concat")
-    (a0, a1, n0), (b0, b1, n1) = res[0][1], res[1][1]
-    assert a0 == 0 and a1 == b0 and b1 == A.shape[0] and 0 < a1 < A.shape[0]
-    assert int(n0) + int(n1) == C.nnz
+    helpers.assert_csr_bitwise(res[0][0], helpers.triple(C), "world2 concat in the shared host buffer")
+    assert res[0][2]["nnz"] == C.nnz and sum(res[0][2]["sub_panels"]) >= 2
+    # gather=False: every rank's sub-panels, interleaved (block-cyclic) and covering the rows once
+    flat = sorted(res[0][1] + res[1][1])
+    assert flat[0][0] == 0 and flat[-1][1] == A.shape[0]
+    assert all(flat[i][1] == flat[i + 1][0] for i in range(len(flat) - 1))
+    assert all(ok and last == size for _p0, _p1, last, size, ok in flat)
+    assert sum(f[3] for f in flat) == C.nnz
+    assert len(res[0][1]) >= 2 and len(res[1][1]) >= 2
+    ub = np.minimum(multi.row_products(A.indptr, A.indices, B.indptr), B.shape[1])
+    assert all(ub[p0:p1].sum() <= 40000 or p1 - p0 == 1 for p0, p1, *_ in flat)
 
 
 def test_split_rows_by_bound():
@@ -170,7 +213,7 @@ def test_spmv_row_panels_world2_gloo():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    assert res[1][0] is None
+    assert np.array_equal(res[1][0], res[0][0])  # y is all-gathered: every rank holds it
     A = helpers.random_csr(301, 170, 0.1, 9)
     A.data[:] = np.arange(A.nnz) % 7 - 3.0
     x = np.random.default_rng(3).standard_normal(170).astype(np.float32)
