@@ -86,10 +86,12 @@ const char *b200sp_status_string(int status);
  * exact nnz of every row of C and writes the final C.indptr into dCp (m+1 int32, device,
  * caller owned - allocated before the call exactly like alg1.cu:156 / cusparse.py:2039).
  *
- *   alg, chunk_fraction : B200SP_ALG1 / DEFAULT = single pass over all rows;
- *       ALG2 / ALG3 = memory bounded mode: rows are processed in chunks that each hold at
- *       most chunk_fraction of the intermediate products, so the spill workspace is bounded
- *       (chunk_fraction in (0,1], default 0.2 as in spgemm_from_txt_alg3.cu:103).
+ *   alg, chunk_fraction : mirrors cuSPARSE's ALG1 / ALG2 / ALG3 knob (chunk_fraction in (0,1],
+ *       default 0.2 as in spgemm_from_txt_alg3.cu:103).  This engine never allocates an
+ *       O(products) buffer: ALG1 already runs at inputs + C + 12 m bytes.  What the chunked modes
+ *       can still bound is (a) here, with device-resident caller-owned C: the CTA-private spill
+ *       workspace of the global-bitmap kernels (their grid shrinks by ceil(1/chunk_fraction));
+ *       (b) in b200sp_spgemm_host with ALG3: C itself - see there.  Bits are identical in all modes.
  *   num_products (host, out, may be NULL): sum_i sum_{k in A_i} nnz(B_k)  (FLOPs / 2).
  *   nnzA, nnzB: stored entries of A and B (what cusparseCreateCsr is given, alg1.cu:149-154).
  *   nnzC (host, out): number of stored entries of C.  One host synchronisation happens here,
@@ -125,6 +127,13 @@ int b200sp_spgemm_numeric(b200sp_handle_t handle, int dtype, const void *alpha, 
  * plus the .get().  The output arrays live in pinned host memory OWNED BY THE HANDLE: they stay
  * valid until the next *_host call on this handle or b200sp_destroy (do not free them).
  * hA* == hB* (aliasing) uploads the matrix once.
+ * alg == B200SP_ALG3: the memory-bounded mode (spgemm_from_txt_alg3.cu:101-115,195-208).  The rows
+ * of C are cut into chunks of at most chunk_fraction * nnz(C) entries (a larger row is a chunk of
+ * its own); chunk c+1 is computed while chunk c is copied to the host, so the device holds two
+ * chunk buffers instead of C: peak = inputs + 2 * chunk + workspace.  The cost is a second
+ * structure pass per chunk and two host synchronisations per chunk.  ALG2 = ALG1 here.
+ * b200sp_stats.peak_workspace_bytes after the call (on a released arena) is the device
+ * high-water mark including the staged inputs and outputs; num_chunks the number of chunks.
  */
 int b200sp_spgemm_host(b200sp_handle_t handle, int dtype, int64_t m, int64_t k, int64_t n,
                        const int32_t *hAp, const int32_t *hAj, const void *hAx, const int32_t *hBp,

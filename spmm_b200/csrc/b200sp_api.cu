@@ -87,6 +87,7 @@ struct b200sp_context {
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaStream_t copy_stream = nullptr;  // second DMA queue of the *_host entry points (ingest pipeline)
   cudaEvent_t ev_copy = nullptr, ev_sym = nullptr;
+  cudaEvent_t ev_slot[2] = {nullptr, nullptr}, ev_chunk = nullptr;  // chunked (ALG3) host entry: output double buffer
   float ms_symbolic = 0.f, ms_numeric = 0.f;
   bool numeric_timed = false;
   Plan plan;
@@ -252,6 +253,8 @@ extern "C" int b200sp_create(b200sp_handle_t *handle, int device) {
   cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
   cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming);
   cudaEventCreateWithFlags(&h->ev_sym, cudaEventDisableTiming);
+  for (auto &e : h->ev_slot) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&h->ev_chunk, cudaEventDisableTiming);
   *handle = h;
   return B200SP_OK;
 }
@@ -279,6 +282,9 @@ extern "C" int b200sp_destroy(b200sp_handle_t h) {
     if (e) cudaEventDestroy(e);
   if (h->ev_copy) cudaEventDestroy(h->ev_copy);
   if (h->ev_sym) cudaEventDestroy(h->ev_sym);
+  for (auto &e : h->ev_slot)
+    if (e) cudaEventDestroy(e);
+  if (h->ev_chunk) cudaEventDestroy(h->ev_chunk);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   delete h;
   return B200SP_OK;
@@ -527,10 +533,11 @@ int run_numeric(b200sp_context *h, const void *alpha, const void *Ax, const void
   int off = 0;
   for (int b = 0; b < p.num_limits.nbins; ++b) {
     const int cnt = p.num_count[b];
-    for (int c = 0; c < p.num_chunks && cnt > 0; ++c) {
-      const int r0 = (int)((int64_t)cnt * c / p.num_chunks), r1 = (int)((int64_t)cnt * (c + 1) / p.num_chunks);
-      if (r1 > r0) TRY(launch_numeric_bin<T>(h, b, p.rows_num + off + r0, r1 - r0, a, (const T *)Ax, (const T *)Bx, Cj, (T *)Cx));
-    }
+    // ALG2 / ALG3 on device-resident operands: C is caller-owned and allocated whole, so the only
+    // memory left to bound is the spill workspace of the global-bitmap kernels - their grid (and
+    // with it the CTA-private workspace) shrinks by num_chunks; every other bin runs as in ALG1
+    // (round 1 cut every bin's row list into num_chunks launches: time for nothing).
+    if (cnt > 0) TRY(launch_numeric_bin<T>(h, b, p.rows_num + off, cnt, a, (const T *)Ax, (const T *)Bx, Cj, (T *)Cx));
     off += cnt;
   }
   return B200SP_OK;
@@ -630,10 +637,7 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
   int off = 0;
   for (int b = 0; b < p.sym_limits.nbins; ++b) {
     const int cnt = p.sym_count[b] = h->h_counters->sym_count[b];
-    for (int c = 0; c < p.num_chunks && cnt > 0; ++c) {
-      const int r0 = (int)((int64_t)cnt * c / p.num_chunks), r1 = (int)((int64_t)cnt * (c + 1) / p.num_chunks);
-      if (r1 > r0) TRY(launch_symbolic_bin(h, b, p.rows_sym + off + r0, r1 - r0));
-    }
+    if (cnt > 0) TRY(launch_symbolic_bin(h, b, p.rows_sym + off, cnt));
     off += cnt;
   }
   // counts -> indptr
@@ -930,11 +934,18 @@ extern "C" int b200sp_spgemm_host(b200sp_handle_t h, int dtype, int64_t m, int64
     cudaStreamSynchronize(cs);  // the caller may free its value arrays as soon as we return
     return rc;
   }
+  // ALG3 = the memory-bounded mode (spgemm_from_txt_alg3.cu:101-115, 195-208: chunk_fraction sizes
+  // the compute buffer).  ALG1 already holds nothing but inputs + C + 12 m bytes, so what is left
+  // to bound is C itself: the rows are cut into chunks of at most chunk_fraction * nnz(C) entries,
+  // chunk c + 1 is computed while chunk c travels to the host, and the device only ever holds two
+  // chunk-sized output buffers.  The price is a second structure pass per chunk (the plan of the
+  // chunk's rows) and 2 host synchronisations per chunk.  ALG2 runs the ALG1 path.
+  const bool chunked = alg == B200SP_ALG3 && nc > 0 && chunk_fraction < 1.f && m > 1;
   rc = ensure_pinned(h, 0, (size_t)(m + 1) * 4);
   if (rc == B200SP_OK) rc = ensure_pinned(h, 1, (size_t)nc * 4);
   if (rc == B200SP_OK) rc = ensure_pinned(h, 2, (size_t)nc * vs);
-  if (rc == B200SP_OK) rc = ensure(h, h->io[7], std::max<size_t>((size_t)nc * 4, 16));
-  if (rc == B200SP_OK) rc = ensure(h, h->io[8], std::max<size_t>((size_t)nc * vs, 16));
+  if (rc == B200SP_OK && !chunked) rc = ensure(h, h->io[7], std::max<size_t>((size_t)nc * 4, 16));
+  if (rc == B200SP_OK && !chunked) rc = ensure(h, h->io[8], std::max<size_t>((size_t)nc * vs, 16));
   if (rc != B200SP_OK) {
     cudaStreamSynchronize(cs);
     return rc;
@@ -944,6 +955,72 @@ extern "C" int b200sp_spgemm_host(b200sp_handle_t h, int dtype, int64_t m, int64
   CUDA_TRY(h, cudaStreamWaitEvent(cs, h->ev_sym, 0));
   CUDA_TRY(h, cudaMemcpyAsync(h->pinned_out[0], h->io[6].ptr, (size_t)(m + 1) * 4, cudaMemcpyDeviceToHost, cs));
   CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->ev_copy, 0));
+  if (chunked) {
+    CUDA_TRY(h, cudaStreamSynchronize(cs));  // the host cuts the chunks from C.indptr
+    const int32_t *cp = (const int32_t *)h->pinned_out[0];
+    const int64_t total_products = h->plan.num_products;
+    const int64_t budget = std::max<int64_t>(1, (int64_t)std::floor((double)chunk_fraction * (double)nc));
+    std::vector<int64_t> cuts(1, 0);
+    int64_t max_chunk = 0, max_rows = 0;
+    for (int64_t r0 = 0; r0 < m;) {
+      // last r1 with cp[r1] - cp[r0] <= budget; a row larger than the budget is a chunk of its own
+      int64_t r1 = std::upper_bound(cp + r0 + 1, cp + m + 1, (int32_t)std::min<int64_t>(cp[r0] + budget, INT32_MAX)) - cp - 1;
+      r1 = std::min<int64_t>(std::max<int64_t>(r1, r0 + 1), m);
+      cuts.push_back(r1);
+      max_chunk = std::max<int64_t>(max_chunk, cp[r1] - cp[r0]);
+      max_rows = std::max<int64_t>(max_rows, r1 - r0);
+      r0 = r1;
+    }
+    rc = ensure(h, h->io[7], std::max<size_t>((size_t)max_chunk * 4 * 2, 16));
+    if (rc == B200SP_OK) rc = ensure(h, h->io[8], std::max<size_t>((size_t)max_chunk * vs * 2, 16));
+    if (rc == B200SP_OK) rc = ensure(h, h->io[9], (size_t)(max_rows + 1) * 4);
+    if (rc != B200SP_OK) return rc;
+    const int *dAp = (const int *)h->io[0].ptr;
+    for (size_t c = 0; c + 1 < cuts.size(); ++c) {
+      const int64_t r0 = cuts[c], r1 = cuts[c + 1];
+      const int64_t want = (int64_t)cp[r1] - cp[r0];
+      if (want == 0) continue;
+      const int slot = (int)(c & 1);
+      int32_t *dj = (int32_t *)h->io[7].ptr + (size_t)slot * max_chunk;
+      char *dx = (char *)h->io[8].ptr + (size_t)slot * max_chunk * vs;
+      int64_t got = 0, np_chunk = 0;
+      // the row panel [r0, r1) of A: same index / value arrays, shifted row pointers (the kernels
+      // only ever read Ap[row] and Ap[row + 1] as absolute positions)
+      rc = b200sp_spgemm_symbolic(h, r1 - r0, k, n, (int64_t)hAp[r1] - hAp[r0], nnzB, dAp + r0, (const int *)h->io[1].ptr,
+                                  (const int *)h->io[bi].ptr, (const int *)h->io[bi + 1].ptr, B200SP_ALG1, 1.f,
+                                  &np_chunk, &got, (int *)h->io[9].ptr);
+      if (rc == B200SP_OK && got != want)
+        rc = fail(h, B200SP_ERR_STATE, "chunk [%lld,%lld): structure pass gave %lld entries, C.indptr says %lld",
+                  (long long)r0, (long long)r1, (long long)got, (long long)want);
+      if (rc != B200SP_OK) {
+        cudaStreamSynchronize(cs);
+        return rc;
+      }
+      CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->ev_slot[slot], 0));  // chunk c - 2 has left this buffer
+      rc = b200sp_spgemm_numeric(h, dtype, alpha, h->io[2].ptr, h->io[bi + 2].ptr, dj, dx);
+      if (rc != B200SP_OK) {
+        cudaStreamSynchronize(cs);
+        return rc;
+      }
+      CUDA_TRY(h, cudaEventRecord(h->ev_chunk, h->stream));
+      CUDA_TRY(h, cudaStreamWaitEvent(cs, h->ev_chunk, 0));
+      CUDA_TRY(h, cudaMemcpyAsync((int32_t *)h->pinned_out[1] + cp[r0], dj, (size_t)want * 4, cudaMemcpyDeviceToHost, cs));
+      CUDA_TRY(h, cudaMemcpyAsync((char *)h->pinned_out[2] + (size_t)cp[r0] * vs, dx, (size_t)want * vs, cudaMemcpyDeviceToHost, cs));
+      CUDA_TRY(h, cudaEventRecord(h->ev_slot[slot], cs));
+    }
+    CUDA_TRY(h, cudaStreamSynchronize(cs));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    h->plan.num_products = total_products;  // report the whole product, not the last chunk
+    h->plan.nnzC = nc;
+    h->plan.num_chunks = (int)cuts.size() - 1;
+    h->plan.valid = false;  // the plan left behind belongs to the last chunk only
+    *hCp = (int32_t *)h->pinned_out[0];
+    *hCj = (int32_t *)h->pinned_out[1];
+    *hCx = h->pinned_out[2];
+    *nnzC = nc;
+    if (num_products) *num_products = total_products;
+    return B200SP_OK;
+  }
   rc = b200sp_spgemm_numeric(h, dtype, alpha, h->io[2].ptr, h->io[bi + 2].ptr, (int *)h->io[7].ptr, h->io[8].ptr);
   if (rc != B200SP_OK) {
     cudaStreamSynchronize(cs);

@@ -213,6 +213,55 @@ def test_host_entry_point(b200):
     assert_csr_bitwise((p, j, x), oracle_spgemm(A, A, alpha=2.0), "host alias")
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_host_alg3_trades_memory_for_chunks(b200, dtype):
+    """ALG3 through the host entry: identical bits, and the device high-water mark (inputs +
+    output staging + workspace, on a fresh arena) drops from |C| to two chunk buffers
+    (spgemm_from_txt_alg3.cu:101-115 chunk_fraction semantics; SpGEMM_alg_comparison's peak-VRAM axis)."""
+    from spmm_b200 import _lib
+    A = helpers.profiler_matrix(2048, 2048, 0.02, dtype=dtype)   # 1.7e6 products, nnz(C) ~ 1.1e6
+    want = oracle_spgemm(A, A)
+    lib, h = _lib.load(), _lib.handle(0)
+    peaks, chunks = {}, {}
+    for alg, cf in ((1, 0.2), (2, 0.2), (3, 0.5), (3, 0.2), (3, 0.05), (3, 1.0)):
+        lib.b200sp_release_workspace(h)
+        lib.b200sp_reset_stats(h)
+        p, j, x, prods = b200.host.spgemm_host(A, A, A.shape + (A.shape[1],), alg=alg, chunk_fraction=cf)
+        assert_csr_bitwise((p, j, x), want, f"host alg={alg} cf={cf}")
+        st = _lib.stats(0)
+        assert prods == st.num_products == int(np.diff(A.indptr)[A.indices].sum())
+        assert st.nnz_c == want[1].size
+        peaks[(alg, cf)], chunks[(alg, cf)] = st.peak_workspace_bytes, st.num_chunks
+    out_bytes = want[1].size * (4 + np.dtype(dtype).itemsize)
+    assert peaks[(2, 0.2)] == peaks[(1, 0.2)] == peaks[(3, 1.0)]
+    assert chunks[(3, 0.2)] >= 5 and chunks[(3, 0.05)] >= 20
+    # two chunk buffers instead of the whole of C
+    assert peaks[(3, 0.2)] <= peaks[(1, 0.2)] - int(0.55 * out_bytes)
+    assert peaks[(3, 0.05)] < peaks[(3, 0.2)] < peaks[(3, 0.5)] <= peaks[(1, 0.2)] + 64 * 1024
+    # one dominant row: it becomes a chunk of its own, nothing is lost
+    S, T = helpers.skewed_pair(k=2000, n=30000)
+    p, j, x, _ = b200.host.spgemm_host(S, T, (S.shape[0], S.shape[1], T.shape[1]), alg=3, chunk_fraction=0.01)
+    assert_csr_bitwise((p, j, x), oracle_spgemm(S, T), "host alg3 skewed")
+
+
+def test_noncanonical_b_is_rejected(b200):
+    """The C ABI and the host entry refuse a B with unsorted / duplicate columns (the kernels
+    rely on distinct columns inside a B row) instead of returning a silently wrong C."""
+    A, B = helpers.grid_case(64, 0.3)
+    bad = B.copy()
+    r = int(np.argmax(np.diff(bad.indptr) >= 2))
+    s0 = bad.indptr[r]
+    bad.indices[s0], bad.indices[s0 + 1] = bad.indices[s0 + 1], bad.indices[s0]   # one unsorted row
+    with pytest.raises(ValueError):
+        b200.host.spgemm_host(A, (bad.indptr, bad.indices, bad.data), (64, 64, 64))
+    dup = B.copy()
+    dup.indices[s0 + 1] = dup.indices[s0]                                         # a duplicate column
+    with pytest.raises(ValueError):
+        b200.host.spgemm_host(A, (dup.indptr, dup.indices, dup.data), (64, 64, 64))
+    p, j, x, _ = b200.host.spgemm_host(A, B, (64, 64, 64))                        # the handle is still usable
+    assert_csr_bitwise((p, j, x), oracle_spgemm(A, B), "after rejection")
+
+
 def test_numeric_reuse_new_values(b200):
     """Same structure, new values: numeric may be called again on the stored plan."""
     import ctypes

@@ -73,7 +73,7 @@ def get(name):
     return MATS[name]
 
 
-@pytest.mark.parametrize("kernel", ["stream", "vector"])
+@pytest.mark.parametrize("kernel", ["auto", "merge", "vector", "merge+scalar", "vector+scalar"])
 @pytest.mark.parametrize("name", ["short_rows", "c2_like", "long_rows", "tiny", "skewed", "tile_aligned"])
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 def test_spmv(b200, name, dtype, kernel, monkeypatch):
@@ -94,6 +94,27 @@ def test_spmv(b200, name, dtype, kernel, monkeypatch):
     bound = 0.5 * (abs(A) @ np.abs(x)) + 0.25 * np.abs(y0) + 1e-30
     tol = 1e-5 if dtype == np.float32 else 1e-13
     assert (np.abs(z.cpu().numpy().astype(np.float64) - want) / bound).max() <= tol
+
+
+def test_spmv_unaligned_arrays(b200, monkeypatch):
+    """Index / value arrays that do not start on a 16-byte boundary (views into larger buffers)
+    must take the 4-byte-load kernels, not the 128-bit ones."""
+    A = get("c2_like")
+    x = np.random.default_rng(9).standard_normal(A.shape[1]).astype(np.float32)
+    want = oracle.spmv(helpers.triple(A), x)
+    dev = torch.device("cuda")
+    for shift in (1, 2, 3):
+        jbuf = torch.empty(A.nnz + 8, dtype=torch.int32, device=dev)
+        xbuf = torch.empty(A.nnz + 8, dtype=torch.float32, device=dev)
+        jbuf[shift:shift + A.nnz] = torch.from_numpy(A.indices).to(dev)
+        xbuf[shift:shift + A.nnz] = torch.from_numpy(A.data).to(dev)
+        a = b200.csr_matrix((xbuf[shift:shift + A.nnz], jbuf[shift:shift + A.nnz], torch.from_numpy(A.indptr).to(dev)),
+                            shape=A.shape)
+        assert a.indices.data_ptr() % 16 != 0
+        for kernel in ("merge", "vector"):
+            monkeypatch.setenv("B200SP_SPMV_KERNEL", kernel)
+            y = b200.cusparse.spmv(a, torch.from_numpy(x).to(dev))
+            check(y.cpu().numpy(), A, x, want, np.float32)
 
 
 def test_spmv_deterministic(b200):
