@@ -611,18 +611,22 @@ def c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, scale
             b = b_res
         ev[1].record()
         chk = torch.zeros(4, dtype=torch.int64, device=dev)
-        ms_num = 0.0
+        ms_num, cev = 0.0, []
         for p0, p1 in mine:
             pp, pj, px = multi.slice_rows(*At, p0, p1)
             a = spmm_b200.csr_matrix((np.ascontiguousarray(px), np.ascontiguousarray(pj), pp), shape=(p1 - p0, n))
             a._canonical = True
             c = spmm_b200.cusparse.spgemm(a, b, alg=args.alg, chunk_fraction=args.chunk_fraction)
             ms_num += _lib.stats(dev.index).ms_numeric
-            chk += device_checksums(torch, p0, c)
+            cev.append((torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)))
+            cev[-1][0].record()
+            chk += device_checksums(torch, p0, c)   # the checker, timed apart and taken out of `ms`
+            cev[-1][1].record()
             del c, a
         ev[2].record()
         torch.cuda.synchronize()
-        return chk, ev[0].elapsed_time(ev[2]), ev[0].elapsed_time(ev[1]), ms_num
+        ms_chk = sum(x.elapsed_time(y) for x, y in cev)
+        return chk, ev[0].elapsed_time(ev[2]) - ms_chk, ev[0].elapsed_time(ev[1]), ms_num
 
     step()
     if world > 1:
@@ -682,7 +686,7 @@ def c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, scale
             "parity": {"checksums": got, "golden": {k: gold[k] for k in got} if gold else None,
                        "checksums_match_golden": (all(got[k] == gold[k] for k in got) if gold else None),
                        "first_rows_of_every_rank_bitwise_vs_scipy": bool(ok.item())},
-            "note": "step = NCCL broadcast of B + H2D of the rank's A sub-panels + symbolic + numeric + device checksums; 1 warm-up, mean of 2"}
+            "note": "step = NCCL broadcast of B + H2D of the rank's A sub-panels + symbolic + numeric of every sub-panel; the device checksums (the parity checker) run between sub-panels and their time is subtracted; 1 warm-up, mean of 2"}
 
 
 # ------------------------------------------------------- C5: R-MAT, streamed row panels ----
@@ -905,13 +909,13 @@ def extras(args, spmm_b200, torch, dev, peak):
         x = torch.from_numpy(xh).to(dev)
         y = torch.empty(M.shape[0], dtype=torch.float32, device=dev)
         nbytes = 4 * (M.shape[0] + 1) + M.nnz * 8 + M.shape[1] * 4 + M.shape[0] * 4
-        for kern in ("auto", "vector", "merge", "vector+scalar", "merge+scalar"):
+        for kern in ("auto", "vector4", "merge", "vector+scalar", "merge+scalar"):
             os.environ["B200SP_SPMV_KERNEL"] = kern
             ms = timed(lambda: spmm_b200.cusparse.spmv(a, x, y=y), 20)
             out[f"spmv_c2_{kern}"] = {"ms": ms, "GBps": nbytes / ms / 1e6, "frac_hbm": nbytes / ms / 1e6 / peak, "nnz": int(M.nnz)}
         os.environ.pop("B200SP_SPMV_KERNEL", None)
         out["spmv_c2_note"] = ("C2 = 2^20 square, 1.1e7 uniformly random nonzeros, fp32, L2 flushed before each run; auto = the library's "
-                               "choice (row-group kernel with 128-bit loads here; merge-path for skewed rows); +scalar = 4-byte loads; "
+                               "choice (row-group kernel here, 4-byte loads below 16 entries per row and 128-bit above; merge-path for skewed rows); vector4 / merge = 128-bit loads; +scalar = 4-byte loads; "
                                "algorithmic bytes = 4(m+1) + 8 nnz + 4n + 4m; x gathers (one 32 B sector per nonzero) bound it, not HBM")
         t0 = time.perf_counter()
         for _ in range(3):

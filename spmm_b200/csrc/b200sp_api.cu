@@ -20,6 +20,7 @@
 #include "spgemm_numeric.cuh"
 #include "spgemm_setup.cuh"
 #include "spgemm_symbolic.cuh"
+#include "spgemm_rank.cuh"
 #include "spmv.cuh"
 #include "csr_utils.cuh"
 #include "convert.cuh"
@@ -34,7 +35,9 @@ constexpr size_t SMEM_DENSE_MAX = 208 * 1024;   // budget for an n-column dense 
 constexpr size_t SMEM_BLOCKED_MAX = 100 * 1024;  // accumulator budget of k_num_dense_pieces: two CTAs per SM (measured best)
 constexpr int DENSE_BLOCKED_MAX_BLOCKS = 384;    // most column blocks it may need (R-MAT scale 22 in fp64: 328)
 constexpr int PIECES_NT = 256;                   // its CTA size = the longest piece of a B row applied per barrier
-constexpr int RANKBM_MAX_N = 32768;             // widest matrix for the bitmap-rank output of the warp bins
+constexpr int RANKBM_MAX_N = 32768;
+constexpr size_t SMEM_RANK_ACC = 96 * 1024;     // compact accumulator of k_num_rank_cta: two CTAs of 256 threads per SM
+constexpr int RANK_NT = 256;             // widest matrix for the bitmap-rank output of the warp bins
 
 struct Buffer {  // grow-only device buffer
   void *ptr = nullptr;
@@ -42,7 +45,7 @@ struct Buffer {  // grow-only device buffer
 };
 
 enum SymKind { SYM_GROUP8, SYM_WARP, SYM_CTA_HASH, SYM_CTA_BITMAP };
-enum NumKind { NUM_GROUP8, NUM_WARP, NUM_CTA_HASH, NUM_GLOBAL, NUM_DENSE, NUM_DENSE_BLOCKED };
+enum NumKind { NUM_GROUP8, NUM_WARP, NUM_CTA_HASH, NUM_GLOBAL, NUM_DENSE, NUM_DENSE_BLOCKED, NUM_RANK };
 
 struct BinPlan {
   int kind;
@@ -378,18 +381,40 @@ void plan_bins(Plan &p) {
     p.num_limits.nbins = 4;
     for (int b = 0; b < 4; ++b) p.num_limits.limit[b] = dl[b];
     p.num_bins[3] = {NUM_DENSE, 0};
-  } else if ((size_t)p.n * 8 <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_BLOCKED_MAX) {
-    // wide matrix: rows with at least ~n/128 entries are worth the column-block walk and go to the
-    // column-blocked dense kernel; an 8 K-slot shared-memory hash keeps the rows below that (the
-    // 16 K-slot table leaves one 8-warp CTA per SM: R-MAT scale 20 runs 10 % faster without it)
-    const int t_dense = std::max(512, std::min(6144, p.n / 128));
+  } else {
+    // wide matrix.  Rows up to t entries keep the 8 K-slot shared-memory hash (the 16 K-slot table
+    // leaves one 8-warp CTA per SM: R-MAT scale 20 runs 10 % faster without it).  Above that:
+    //   rank    - compact rank accumulator (k_num_rank_cta): passes = ceil(nnz(C_i) / CAP), B rows applied whole
+    //   blocked - dense column blocks (k_num_dense_pieces): ceil(n / W) blocks per row
+    // B200SP_HEAVY = rank | blocked | mixed (rank up to n / B200SP_HEAVY_DENSE_DIV entries, blocked for the
+    // denser rows); B200SP_HEAVY_MIN overrides t.
+    const char *mode = getenv("B200SP_HEAVY");
+    const char *tmin = getenv("B200SP_HEAVY_MIN");
+    const char *ddiv = getenv("B200SP_HEAVY_DENSE_DIV");
+    const bool blocked_ok = (size_t)p.n * 8 <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_BLOCKED_MAX;
+    const bool want_blocked = blocked_ok && mode && strcmp(mode, "blocked") == 0;
+    const bool want_mixed = blocked_ok && mode && strcmp(mode, "mixed") == 0;
+    int t_dense = std::max(512, std::min(6144, p.n / 128));
+    if (tmin && atoi(tmin) >= 512) t_dense = std::min(6144, atoi(tmin));
     int nb = 3;
     if (t_dense > 512) {
       p.num_limits.limit[nb] = t_dense;
       p.num_bins[nb++] = {NUM_CTA_HASH, 8192};
     }
-    p.num_limits.limit[nb] = INT_MAX;
-    p.num_bins[nb++] = {NUM_DENSE_BLOCKED, 0};
+    if (want_blocked) {
+      p.num_limits.limit[nb] = INT_MAX;
+      p.num_bins[nb++] = {NUM_DENSE_BLOCKED, 0};
+    } else if (want_mixed) {
+      const int div = ddiv && atoi(ddiv) > 0 ? atoi(ddiv) : 8;
+      const int t_rank = std::max(t_dense + 1, p.n / div);
+      p.num_limits.limit[nb] = t_rank;
+      p.num_bins[nb++] = {NUM_RANK, 0};
+      p.num_limits.limit[nb] = INT_MAX;
+      p.num_bins[nb++] = {NUM_DENSE_BLOCKED, 0};
+    } else {
+      p.num_limits.limit[nb] = INT_MAX;
+      p.num_bins[nb++] = {NUM_RANK, 0};
+    }
     p.num_limits.nbins = nb;
   }
 }
@@ -514,6 +539,28 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         return check_launch(h, "k_num_dense_pieces");
       }
       // B not canonical (or absurdly wide): the global-memory kernel takes any input
+      goto global_fallback;
+    case NUM_RANK: {
+      size_t acc_bytes = SMEM_RANK_ACC;
+      if (const char *kb = getenv("B200SP_RANK_ACC_KB")) {
+        const long v = atol(kb);
+        if (v >= 8 && v <= 200) acc_bytes = (size_t)v * 1024;
+      }
+      const int CAP = (int)(acc_bytes / sizeof(T)) & ~31;
+      const size_t smem = (size_t)CAP * sizeof(T);
+      TRY(set_smem(h, k_num_rank_cta<T, RANK_NT>, smem));
+      int per_sm = 1;
+      CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_rank_cta<T, RANK_NT>, RANK_NT, smem));
+      const int grid = std::max(1, std::min(cnt, h->num_sms * std::max(1, per_sm) / (p.num_chunks > 1 ? 2 : 1)));
+      const size_t nwords = (size_t)((p.n + 31) / 32);
+      TRY(ensure(h, h->ws2, (size_t)grid * nwords * sizeof(uint2)));  // {bits, prefix} per 32 columns and CTA
+      TRY(ensure(h, h->ws3, 256));
+      CUDA_TRY(h, cudaMemsetAsync(h->ws2.ptr, 0, (size_t)grid * nwords * sizeof(uint2), st));
+      CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, sizeof(int), st));  // rows are handed out by ticket
+      k_num_rank_cta<T, RANK_NT><<<grid, RANK_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, CAP, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, p.Cp, Cj, Cx, alpha, (uint2 *)h->ws2.ptr);
+      return check_launch(h, "k_num_rank_cta");
+    }
+    global_fallback:
     case NUM_GLOBAL: {
       const size_t bytes = (size_t)((p.n + 31) / 32) * 8;  // bitmap + prefix
       int grid = std::max(1, std::min(cnt, 2 * h->num_sms / p.num_chunks));
@@ -707,12 +754,14 @@ int run_spmv(b200sp_context *h, int m, int n, int64_t nnz, int64_t ncols, const 
   // similar length (C2: 67 us vs 75 us merge-path); merge-path when one row can hold a warp up
   // (R-MAT scale 20, longest row 39 705: 89 us vs 1875 us).  The longest row is measured once per
   // matrix (one small kernel + a 4-byte D2H) and cached on the handle.
-  // B200SP_SPMV_KERNEL = vector | merge forces one; "+scalar" (e.g. "merge+scalar") forces the
-  // 4-byte-load variants (what bench.py uses to report both).
+  // B200SP_SPMV_KERNEL = vector | vector4 | merge forces one (vector4 = the 128-bit row-group kernel
+  // whatever the row length); "+scalar" (e.g. "merge+scalar") forces the 4-byte-load variants (what
+  // bench.py uses to report all of them).
   const char *mode = getenv("B200SP_SPMV_KERNEL");
   const bool force_vector = mode && strncmp(mode, "vector", 6) == 0;
   const bool force_merge = mode && (strncmp(mode, "merge", 5) == 0 || strncmp(mode, "tile", 4) == 0);
   const bool scalar_only = mode && strstr(mode, "scalar") != nullptr;
+  const bool force_vec4 = mode && strncmp(mode, "vector4", 7) == 0;
   const bool aligned = (((uintptr_t)Aj | (uintptr_t)Ax) & 15) == 0;
   const bool vec = aligned && !scalar_only;
   bool use_merge = ncols == 1 && nnz > 0;
@@ -757,7 +806,9 @@ int run_spmv(b200sp_context *h, int m, int n, int64_t nnz, int64_t ncols, const 
     return check_launch(h, "k_spmv_fixup");
   }
   const double avg = (double)nnz / (double)m;
-  if (vec) {  // four entries per lane and trip: a quarter of the lanes per row
+  // 128-bit loads pay once a row fills a few 4-entry lanes; on C2 (10.5 entries per row, unaligned
+  // row starts) half of every 16-byte load is masked and the scalar kernel is 8 % faster (66 vs 72 us)
+  if (vec && (force_vec4 || avg >= 16.0)) {  // four entries per lane and trip: a quarter of the lanes per row
     const int G = avg <= 3 ? 1 : avg <= 6 ? 2 : avg <= 12 ? 4 : avg <= 24 ? 8 : avg <= 48 ? 16 : 32;
     const int gx = std::max(1, std::min((int)(((int64_t)m + 256 / G - 1) / (256 / G)), h->num_sms * 16));
     dim3 grid(gx, (unsigned)ncols);

@@ -50,7 +50,7 @@ def c2():
     return A, x, want, bound
 
 
-@pytest.mark.parametrize("kernel", ["auto", "vector", "merge", "vector+scalar", "merge+scalar"])
+@pytest.mark.parametrize("kernel", ["auto", "vector", "vector4", "merge", "vector+scalar", "merge+scalar"])
 def test_c2_spmv_full_size(b200, c2, kernel, monkeypatch):
     """|got - want| <= 1e-5 * sum_j |a_ij x_j| per row (fp32; the sum order differs from the
     sequential CPU loop, see tests/test_gpu_spmv.py)."""

@@ -168,6 +168,29 @@ def test_heavy_rows_hubs_and_hot_columns(b200, dtype, alg, cf):
     assert_csr_bitwise(dev_spgemm(b200, A, B, alg=alg, chunk_fraction=cf), got, "hubs rerun")
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("mode,acc_kb,tmin", [("rank", None, None), ("rank", "8", None), ("rank", "16", "512"),
+                                             ("blocked", None, None), ("mixed", "8", None)])
+def test_heavy_row_kernels_all_modes(b200, dtype, mode, acc_kb, tmin, monkeypatch):
+    """The heavy rows of wide matrices through every kernel choice: the compact rank accumulator
+    (k_num_rank_cta; default), forced into many passes per row by a small accumulator (8 KB = 2048
+    fp32 ranks per pass against rows of up to 80 K entries: the windowed B-row segments and the
+    pass boundaries), the dense column blocks of round 1 (k_num_dense_pieces) and the mix of both.
+    All must give scipy's bits."""
+    monkeypatch.setenv("B200SP_HEAVY", mode)
+    if acc_kb:
+        monkeypatch.setenv("B200SP_RANK_ACC_KB", acc_kb)
+    if tmin:
+        monkeypatch.setenv("B200SP_HEAVY_MIN", tmin)
+    if mode == "mixed":
+        monkeypatch.setenv("B200SP_HEAVY_DENSE_DIV", "16")
+    for name, (A, B) in {"hubs": helpers.hub_pair(dtype=dtype), "skewed": helpers.skewed_pair(dtype=dtype)}.items():
+        want = oracle_spgemm(A, B)
+        got = dev_spgemm(b200, A, B)
+        assert_csr_bitwise(got, want, f"{name} {mode} acc={acc_kb}")
+        assert_csr_bitwise(dev_spgemm(b200, A, B, alpha=0.5), oracle_spgemm(A, B, alpha=0.5), f"{name} {mode} alpha")
+
+
 def test_rmat16_bitwise(b200):
     """R-MAT scale 16 A @ A (4.0e8 products, nnz(C) 1.6e8, n = 65 536 > one accumulator): the C5
     recipe at the largest scale the oracle finishes in seconds."""
@@ -239,7 +262,7 @@ def test_host_alg3_trades_memory_for_chunks(b200, dtype):
     assert peaks[(3, 0.2)] <= peaks[(1, 0.2)] - int(0.55 * out_bytes)
     assert peaks[(3, 0.05)] < peaks[(3, 0.2)] < peaks[(3, 0.5)] <= peaks[(1, 0.2)] + 64 * 1024
     # one dominant row: it becomes a chunk of its own, nothing is lost
-    S, T = helpers.skewed_pair(k=2000, n=30000)
+    S, T = helpers.skewed_pair(k=4500, n=30000)
     p, j, x, _ = b200.host.spgemm_host(S, T, (S.shape[0], S.shape[1], T.shape[1]), alg=3, chunk_fraction=0.01)
     assert_csr_bitwise((p, j, x), oracle_spgemm(S, T), "host alg3 skewed")
 

@@ -73,7 +73,7 @@ def get(name):
     return MATS[name]
 
 
-@pytest.mark.parametrize("kernel", ["auto", "merge", "vector", "merge+scalar", "vector+scalar"])
+@pytest.mark.parametrize("kernel", ["auto", "merge", "vector", "vector4", "merge+scalar", "vector+scalar"])
 @pytest.mark.parametrize("name", ["short_rows", "c2_like", "long_rows", "tiny", "skewed", "tile_aligned"])
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 def test_spmv(b200, name, dtype, kernel, monkeypatch):
@@ -111,7 +111,7 @@ def test_spmv_unaligned_arrays(b200, monkeypatch):
         a = b200.csr_matrix((xbuf[shift:shift + A.nnz], jbuf[shift:shift + A.nnz], torch.from_numpy(A.indptr).to(dev)),
                             shape=A.shape)
         assert a.indices.data_ptr() % 16 != 0
-        for kernel in ("merge", "vector"):
+        for kernel in ("merge", "vector4"):
             monkeypatch.setenv("B200SP_SPMV_KERNEL", kernel)
             y = b200.cusparse.spmv(a, torch.from_numpy(x).to(dev))
             check(y.cpu().numpy(), A, x, want, np.float32)
