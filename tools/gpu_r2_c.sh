@@ -1,0 +1,14 @@
+#!/bin/bash
+# round 2, GPU call C: full GPU test suite, N=1 bench + reference arm, launch list, ncu --set full of the C3 numeric/symbolic kernels
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,memory.total --format=csv > gpurun_out/c_gpu.txt
+( time timeout 1800 python -m pytest tests -m gpu -x -q ) > gpurun_out/c_pytest.txt 2>&1
+echo "pytest rc=$?" >> gpurun_out/c_pytest.txt
+( time timeout 900 python bench.py ) > gpurun_out/c_bench_n1.json 2> gpurun_out/c_bench_n1.err
+echo "bench rc=$?" >> gpurun_out/c_bench_n1.err
+( time timeout 600 python bench.py --impl reference ) > gpurun_out/c_bench_ref.json 2> gpurun_out/c_bench_ref.err
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/c_launches.csv \
+   python bench.py --steps 2 --warmup 1 --no-cpu --no-extra --no-c5 > gpurun_out/c_ncu_launches.log 2>&1
+REPS=3 timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k_num_dense_cta|k_sym_flags_cta" -s 2 -c 2 \
+   -o gpurun_out/c_ncu_c3 -f python tools/profile_cases.py c3_1e-2 > gpurun_out/c_ncu_c3.log 2>&1
+ls -la gpurun_out > gpurun_out/c_ls.txt
