@@ -182,6 +182,29 @@ int b200sp_spmm(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t
                 const void *dB, int64_t ldb, void *dC, int64_t ldc, const void *alpha,
                 const void *beta);
 
+/*
+ * Allocation-free SpMV: y = alpha * A @ x + beta * y like b200sp_spmv, always with the merge-path
+ * kernels, with their per-tile scratch in a fixed device array inside the library instead of the
+ * handle's workspace.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot reach cudaMalloc (code under CUDA stream capture, serving
+ * loops, harnesses that forbid it).  The call performs no cudaMalloc / cudaFree / allocating
+ * library call; inputs and outputs are the caller's device arrays as in b200sp_spmv.
+ *   limit: m + nnz <= B200SP_NOALLOC_MAX_TILES * 2048 (= 2^27) merge items; larger problems are
+ *       rejected with B200SP_ERR_INVALID (message in b200sp_last_error) - use b200sp_spmv.
+ *   cost: every GPU that loads the library holds the B200SP_NOALLOC_SCRATCH_BYTES array until exit.
+ *   sharing: all calls on a device use the same array, which keeps the last call's contents
+ *       (nothing in it needs to start at zero, every word that is read was written by the same
+ *       call); calls that OVERLAP on the GPU - different streams, handles or threads - race.
+ *   The first call on a device resolves the array's device address (cudaGetSymbolAddress); make
+ *   one call before starting a stream capture.
+ * Results are bit-identical to b200sp_spmv with the merge-path kernel (B200SP_SPMV_KERNEL=merge).
+ */
+#define B200SP_NOALLOC_MAX_TILES 65536
+#define B200SP_NOALLOC_SCRATCH_BYTES 2359552
+int b200sp_spmv_noalloc(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t nnz,
+                        const int32_t *dAp, const int32_t *dAj, const void *dAx, const void *dx,
+                        void *dy, const void *alpha, const void *beta);
+
 /* Host-buffer one-shot SpMV (H2D of A and x, kernel, D2H of y): the profilers' timed closure
  * `to_gpu_sparse(A); cp.asarray(C); A_gpu @ C_gpu` (SpGEMM_vs_SpMV/profiler.py:490-493). */
 int b200sp_spmv_host(b200sp_handle_t handle, int dtype, int64_t m, int64_t n, int64_t nnz,

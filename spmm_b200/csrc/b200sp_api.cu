@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -194,6 +195,7 @@ int check_launch(b200sp_context *h, const char *what) {
 }
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+constexpr size_t align_up_c(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct DeviceGuard {
   int prev = -1;
@@ -860,6 +862,99 @@ extern "C" int b200sp_spmv(b200sp_handle_t h, int dtype, int64_t m, int64_t n, i
                            const int32_t *dAj, const void *dAx, const void *dx, void *dy, const void *alpha,
                            const void *beta) {
   return b200sp_spmm(h, dtype, m, n, nnz, 1, dAp, dAj, dAx, dx, n, dy, m, alpha, beta);
+}
+
+// ----------------------------------------------------- SpMV without any allocation ----
+// Merge-path SpMV whose per-tile scratch (tile boundary rows, tile info, head / carry partials)
+// lives in a file-scope device array instead of the handle's workspace, for callers that must not
+// reach cudaMalloc (stream capture, serving loops).  Every GPU that loads the library holds the
+// array (B200SP_NOALLOC_SCRATCH_BYTES) until exit.  All calls on a device share it: calls that
+// overlap on the GPU (two streams, two handles, two threads) race.  Nothing in it has to start at
+// zero - k_spmv_partition writes every boundary, k_spmv_merge writes info[k] of every tile, and
+// k_spmv_fixup reads head / carry entries only where this launch's info says they were written -
+// so the previous call's contents are simply overwritten.
+namespace {
+
+constexpr size_t NOALLOC_O_INFO = align_up_c((size_t)(B200SP_NOALLOC_MAX_TILES + 1) * sizeof(int), 256);
+constexpr size_t NOALLOC_O_HEAD = NOALLOC_O_INFO + align_up_c((size_t)B200SP_NOALLOC_MAX_TILES * sizeof(b200sp::SpmvTileInfo), 256);
+constexpr size_t NOALLOC_O_CARRY = NOALLOC_O_HEAD + align_up_c((size_t)B200SP_NOALLOC_MAX_TILES * sizeof(double), 256);
+constexpr size_t NOALLOC_BYTES = NOALLOC_O_CARRY + align_up_c((size_t)B200SP_NOALLOC_MAX_TILES * sizeof(double), 256);
+static_assert(NOALLOC_BYTES == B200SP_NOALLOC_SCRATCH_BYTES, "include/b200sp.h states the size of the scratch array");
+
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+namespace {
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+void *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};  // device address of g_noalloc_scratch, per device
+
+// In host code `g_noalloc_scratch` is only the host-side shadow of the symbol; the address a
+// kernel may use comes from cudaGetSymbolAddress with the owning device current (resolved once per
+// device, at the first call).
+int noalloc_scratch(b200sp_context *h, char **out) {
+  if (h->device < 0 || h->device >= NOALLOC_MAX_DEVICES) return fail(h, B200SP_ERR_INVALID, "device %d out of range", h->device);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[h->device]) {
+    int cur = -1;
+    CUDA_TRY(h, cudaGetDevice(&cur));
+    if (cur != h->device) return fail(h, B200SP_ERR_STATE, "device %d is not current (%d is)", h->device, cur);
+    void *p = nullptr;
+    CUDA_TRY(h, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p) return fail(h, B200SP_ERR_CUDA, "cudaGetSymbolAddress returned NULL");
+    g_noalloc_ptr[h->device] = p;
+  }
+  *out = (char *)g_noalloc_ptr[h->device];
+  return B200SP_OK;
+}
+
+template <typename T>
+int run_spmv_noalloc(b200sp_context *h, int m, int64_t nnz, const int *Ap, const int *Aj, const T *Ax, const T *x,
+                     T *y, const void *alpha, const void *beta) {
+  const T a = alpha ? *(const T *)alpha : T(1);
+  const T b = beta ? *(const T *)beta : T(0);
+  const long long total = (long long)m + nnz;
+  const long long ntiles_ll = (total + SPMV_TILE - 1) / SPMV_TILE;
+  if (ntiles_ll > B200SP_NOALLOC_MAX_TILES)
+    return fail(h, B200SP_ERR_INVALID,
+                "b200sp_spmv_noalloc: m + nnz = %lld exceeds the fixed scratch (%lld merge items = %d tiles of %d); "
+                "use b200sp_spmv", total, (long long)B200SP_NOALLOC_MAX_TILES * SPMV_TILE, B200SP_NOALLOC_MAX_TILES,
+                SPMV_TILE);
+  const int ntiles = (int)ntiles_ll;
+  char *base = nullptr;
+  TRY(noalloc_scratch(h, &base));
+  int *tile_row = (int *)base;
+  SpmvTileInfo *info = (SpmvTileInfo *)(base + NOALLOC_O_INFO);
+  T *head = (T *)(base + NOALLOC_O_HEAD), *carry = (T *)(base + NOALLOC_O_CARRY);
+  cudaStream_t st = h->stream;
+  const bool vec = (((uintptr_t)Aj | (uintptr_t)Ax) & 15) == 0;
+  k_spmv_partition<<<(ntiles + 1 + 7) / 8, 256, 0, st>>>(m, total, ntiles, Ap, tile_row);
+  TRY(check_launch(h, "k_spmv_partition"));
+  if (vec) k_spmv_merge<T, true><<<ntiles, SPMV_THREADS, 0, st>>>(m, (int)nnz, tile_row, Ap, Aj, Ax, x, y, a, b, info, head, carry);
+  else k_spmv_merge<T, false><<<ntiles, SPMV_THREADS, 0, st>>>(m, (int)nnz, tile_row, Ap, Aj, Ax, x, y, a, b, info, head, carry);
+  TRY(check_launch(h, "k_spmv_merge"));
+  if (ntiles == 1) return B200SP_OK;
+  k_spmv_fixup<T><<<(ntiles + 255) / 256, 256, 0, st>>>(ntiles, info, head, carry, y, a, b);
+  return check_launch(h, "k_spmv_fixup");
+}
+
+}  // namespace
+
+extern "C" int b200sp_spmv_noalloc(b200sp_handle_t h, int dtype, int64_t m, int64_t n, int64_t nnz,
+                                   const int32_t *dAp, const int32_t *dAj, const void *dAx, const void *dx,
+                                   void *dy, const void *alpha, const void *beta) {
+  if (!h) return B200SP_ERR_INVALID;
+  if (m < 0 || n < 0 || nnz < 0 || m >= INT32_MAX || n >= INT32_MAX || nnz > INT32_MAX)
+    return fail(h, B200SP_ERR_INVALID, "bad shape m=%lld n=%lld nnz=%lld", (long long)m, (long long)n, (long long)nnz);
+  if (dtype != B200SP_R_32F && dtype != B200SP_R_64F) return fail(h, B200SP_ERR_INVALID, "unsupported dtype %d", dtype);
+  if (m == 0) return B200SP_OK;
+  if (!dAp || !dy || (nnz && (!dAj || !dAx || !dx))) return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  DeviceGuard guard(h->device);
+  if (dtype == B200SP_R_32F)
+    return run_spmv_noalloc<float>(h, (int)m, nnz, dAp, dAj, (const float *)dAx, (const float *)dx, (float *)dy, alpha, beta);
+  return run_spmv_noalloc<double>(h, (int)m, nnz, dAp, dAj, (const double *)dAx, (const double *)dx, (double *)dy, alpha, beta);
 }
 
 // ==================================================================== canonical helpers ====
