@@ -322,6 +322,10 @@ def run_ours(args):
         for _ in range(max(args.warmup, 3)):
             c = step(bcast)
         nnz_panel = c.nnz
+        # bytes actually allocated for C: the single-pass mode allocates indices / data at the bound
+        # sum_i min(products_i, n) and returns views of nnz(C) entries
+        c_alloc = int(c.indptr.untyped_storage().nbytes() + c.indices.untyped_storage().nbytes() + c.data.untyped_storage().nbytes())
+        single_pass = c.indices.untyped_storage().nbytes() > c.indices.numel() * 4
         del c
         torch.cuda.synchronize()
         if world > 1:
@@ -351,7 +355,8 @@ def run_ours(args):
         ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
         return {"ms_job": _max_over_ranks(torch, dist, dev, world, ms), "ms_num": float(np.mean(ms_num)),
                 "ms_sym": float(np.mean(ms_sym)), "wall": wall, "clocks": clocks, "nnz_panel": nnz_panel,
-                "launches": int(st1.kernel_launches - st0.kernel_launches), "peak_ws": int(st1.peak_workspace_bytes)}
+                "launches": int(st1.kernel_launches - st0.kernel_launches), "peak_ws": int(st1.peak_workspace_bytes),
+                "c_alloc": c_alloc, "single_pass": bool(single_pass)}
 
     main_run = timed_steps(True, True)           # N > 1: B broadcast inside every step
     outside = timed_steps(False, False) if world > 1 else None
@@ -459,12 +464,15 @@ def run_ours(args):
                    "canonical_check": "preset (_canonical = True): the has_canonical_format kernel the reference runs once per matrix is outside the timed step; B's canonical form IS verified inside every step (k_csr_check_canonical)",
                    "op_bytes_algorithmic_rank0_panel": num_bytes,
                    "ms_symbolic": main_run["ms_sym"], "ms_numeric": ms_n, "wall_s_timed_region": main_run["wall"],
+                   "mode": "single pass (b200sp_spgemm_estimate + b200sp_spgemm_single_pass)" if main_run["single_pass"] else "two pass (symbolic + numeric)",
                    "build": build_info()},
         "clocks": main_run["clocks"],
         "e2e": {"value": e2e_val, "unit": "GFLOP/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": t_e2e * 1e3, "steps": e2e_steps, "api": e2e_api},
         "gpu_launches": main_run["launches"],
-        "roofline": {"bound": "hbm", "kernel": "numeric pass (all numeric-bin kernels of one step)", "achieved": achieved,
+        "roofline": {"bound": "hbm", "kernel": ("single-pass kernel k_num_dense_cta<T, single> (structure + values in one walk of the products; "
+                                                "ms_symbolic = the estimate in front of it)" if main_run["single_pass"]
+                                                else "numeric pass (all numeric-bin kernels of one step)"), "achieved": achieved,
                      "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                      "frac_whole_op": num_bytes / (ms_job * 1e-3) / 1e9 / peak,
                      "frac_dram": (traffic / (ms_n * 1e-3) / 1e9 / peak) if (traffic and ms_n > 0) else None,
@@ -473,8 +481,9 @@ def run_ours(args):
                              "frac_whole_op divides by the whole step (symbolic + numeric" + (" + B broadcast" if world > 1 else "") + "); "
                              "frac_dram = ncu dram bytes of the numeric kernel / its time: B is L2-resident, so DRAM sees little but C"},
         "peak_vram": {"workspace_bytes_peak": main_run["peak_ws"], "inputs_bytes": in_bytes, "output_bytes": out_bytes,
-                      "total_beyond_inputs": main_run["peak_ws"] + out_bytes,
-                      "note": "total_beyond_inputs = library workspace high-water mark + C: the quantity the reference samples as dPeak VRAM with inputs resident (dense_vs_sparseGEMM/utils.py:247-250); cuSPARSE's are in extra.cusparse"},
+                      "output_bytes_allocated": main_run["c_alloc"],
+                      "total_beyond_inputs": main_run["peak_ws"] + main_run["c_alloc"],
+                      "note": "total_beyond_inputs = library workspace high-water mark + the bytes ALLOCATED for C (single-pass mode: C.indices / C.data sized at the bound sum_i min(products_i, n), of which output_bytes are used): the quantity the reference samples as dPeak VRAM with inputs resident (dense_vs_sparseGEMM/utils.py:247-250); cuSPARSE's are in extra.cusparse"},
     }
     if world == 1 and not args.no_cpu:
         rows = pick_sample_rows(A)
@@ -855,7 +864,8 @@ def cusparse_table(spmm_b200, torch, _lib):
                 if i >= 2:
                     ts.append(e0.elapsed_time(e1))
             st = _lib.stats(torch.cuda.current_device())
-            row[f"ours_alg{alg}"] = {"ms": float(np.median(ts)), "peak_bytes_beyond_inputs": int(st.peak_workspace_bytes + 4 * (A.shape[0] + 1) + c.nnz * 8)}
+            row[f"ours_alg{alg}"] = {"ms": float(np.median(ts)), "peak_bytes_beyond_inputs": int(st.peak_workspace_bytes + c.indptr.untyped_storage().nbytes() + c.indices.untyped_storage().nbytes() + c.data.untyped_storage().nbytes()),
+                                    "mode": "single pass" if c.indices.untyped_storage().nbytes() > c.indices.numel() * 4 else "two pass"}
             del c
         # host entry: ALG1 holds all of C on the device, ALG3 two chunks of it (device high-water mark, inputs included)
         from spmm_b200 import host
@@ -875,7 +885,7 @@ def cusparse_table(spmm_b200, torch, _lib):
         row["products"], row["nnzA"] = prods, int(A.nnz)
         out[name] = row
     out["note"] = ("ms: device-resident inputs, median of 5; peak_bytes_beyond_inputs = live device allocations above the inputs "
-                   "(cuSPARSE: buffers 1/2/3 + C; ours: workspace + C).  ours_host_alg*: b200sp_spgemm_host wall time with host "
+                   "(cuSPARSE: buffers 1/2/3 + C; ours: workspace + the bytes allocated for C - alg 1 = default mode, which takes the single-pass kernel with C allocated at the bound sum_i min(products_i, n) when C is well filled; alg 3 = two passes, C allocated exactly).  ours_host_alg*: b200sp_spgemm_host wall time with host "
                    "buffers; ALG3 chunks C at chunk_fraction 0.2 so the device holds two chunks instead of C")
     return out
 

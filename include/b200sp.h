@@ -104,6 +104,43 @@ int b200sp_spgemm_symbolic(b200sp_handle_t handle, int64_t m, int64_t k, int64_t
                            const int32_t *dBp, const int32_t *dBj, int alg, float chunk_fraction,
                            int64_t *num_products, int64_t *nnzC, int32_t *dCp);
 
+/* OR-ed into `alg` of b200sp_spgemm_symbolic: the b200sp_spgemm_estimate that has just run on this
+ * handle with exactly these arguments already did the first half (products per row, bins, canonical
+ * check of B); it is not repeated.  B200SP_ERR_STATE when no such estimate is pending. */
+#define B200SP_ALG_REUSE_ESTIMATE 0x100
+
+/*
+ * Single-pass SpGEMM for well-filled C, in two calls.  The reference's cuSPARSE sequence computes
+ * the product into temporary buffers sized from an estimate and copies it out afterwards
+ * (cusparseSpGEMM_workEstimation / _compute / _copy: spgemm_from_txt_alg1.cu:171-188,
+ * cusparse.py:2061-2137); cuSPARSE's ALG1 is the variant that spends memory to save time.  This is
+ * that trade here: C.indices / C.data are allocated at an UPPER BOUND of nnz(C) and the products
+ * are walked once instead of twice.
+ *
+ * b200sp_spgemm_estimate: products per row of A @ B (replaces workEstimation + getNumProducts,
+ *   spgemm_from_txt_alg3.cu:182-191) and from them
+ *     *nnz_bound  = sum_i min(products_i, n) >= nnz(C)  (<= 1.6 nnz(C) for uniformly random operands),
+ *     *single_pass = 1 when the single-pass kernel applies and pays: alg is not a chunked mode, an
+ *       n-column accumulator of `dtype` fits shared memory, the bound fits int32, and the product
+ *       count is at least a quarter of m * n (rows of C well filled; measured cross-over).
+ *   dCp (m+1 int32, caller owned) is the C.indptr the following call fills.  One host sync.
+ *   Then EITHER b200sp_spgemm_single_pass (only if *single_pass), OR b200sp_spgemm_symbolic with
+ *   alg | B200SP_ALG_REUSE_ESTIMATE and the same arguments, followed by b200sp_spgemm_numeric.
+ * b200sp_spgemm_single_pass: fills dCp, dCj, dCx (capacity >= *nnz_bound entries each) and returns
+ *   the exact *nnzC; entries [nnzC, capacity) are left untouched - the caller trims (a view is
+ *   enough, nothing is moved).  Rows are produced in row order by one persistent kernel: a row's
+ *   offset is the total of the rows before it, obtained by decoupled look-back over per-row status
+ *   words, so no separate structure pass, scan or binning runs.  Same bits as the two-pass path.
+ *   One host sync (nnzC), like cusparseSpMatGetSize.
+ */
+int b200sp_spgemm_estimate(b200sp_handle_t handle, int dtype, int64_t m, int64_t k, int64_t n,
+                           int64_t nnzA, int64_t nnzB, const int32_t *dAp, const int32_t *dAj,
+                           const int32_t *dBp, const int32_t *dBj, int alg, float chunk_fraction,
+                           int32_t *dCp, int64_t *num_products, int64_t *nnz_bound, int *single_pass);
+int b200sp_spgemm_single_pass(b200sp_handle_t handle, int dtype, const void *alpha, const void *dAx,
+                              const void *dBx, int32_t *dCj, void *dCx, int64_t capacity,
+                              int64_t *nnzC);
+
 /*
  * Numeric phase: fills dCj (nnzC int32) and dCx (nnzC values), both caller owned, allocated
  * after reading nnzC exactly like cusparse.py:2128-2131 / alg1.cu:184-186.

@@ -15,6 +15,7 @@ OK = 0
 ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_OVERFLOW, ERR_STATE, ERR_IO = -1, -2, -3, -4, -5, -6
 R_32F, R_64F = 0, 1
 ORDER_ROW, ORDER_COL = 0, 1
+ALG_REUSE_ESTIMATE = 0x100
 MAX_BINS = 16
 
 c_i64 = ctypes.c_int64
@@ -46,6 +47,10 @@ SYMBOLS = [
     ("b200sp_spgemm_symbolic", ctypes.c_int,
      [c_vp, c_i64, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, ctypes.c_int, ctypes.c_float,
       i64p, i64p, c_vp]),
+    ("b200sp_spgemm_estimate", ctypes.c_int,
+     [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, ctypes.c_int, ctypes.c_float,
+      c_vp, i64p, i64p, ctypes.POINTER(ctypes.c_int)]),
+    ("b200sp_spgemm_single_pass", ctypes.c_int, [c_vp, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, i64p]),
     ("b200sp_spgemm_numeric", ctypes.c_int, [c_vp, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp]),
     ("b200sp_spgemm_host", ctypes.c_int,
      [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_int,

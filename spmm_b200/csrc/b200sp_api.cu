@@ -66,6 +66,9 @@ struct Plan {
   int sym_count[MAX_BINS]{}, num_count[MAX_BINS]{};
   int *rows_sym = nullptr, *rows_num = nullptr;  // device, inside ws
   int64_t num_products = 0, nnzC = 0, max_row_products = 0;
+  bool stage1 = false;      // row products / bound / symbolic bins of the current arguments are in ws (estimate ran)
+  bool single_pass = false; // the estimate chose the single-pass kernel
+  int64_t nnz_bound = 0;    // sum_i min(products_i, n)
   bool b_canonical = true;  // B rows verified sorted (needed by the column-blocked dense kernel)
   int bounds_nblk = 0, bounds_W = 0;  // geometry of the per-B-row block-boundary table now in ws3 (0 = none)
 };
@@ -394,7 +397,10 @@ void plan_bins(Plan &p) {
     const char *tmin = getenv("B200SP_HEAVY_MIN");
     const char *ddiv = getenv("B200SP_HEAVY_DENSE_DIV");
     const bool blocked_ok = (size_t)p.n * 8 <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_BLOCKED_MAX;
-    const bool want_blocked = blocked_ok && mode && strcmp(mode, "blocked") == 0;
+    // default: blocked.  Measured on B200 (profiles/r02_heavy_modes_v16.jsonl, whole A @ A incl. symbolic):
+    // R-MAT scale 16 / 18 / 20: blocked 7.3 / 56 / 698 ms, rank (96 KB) 9.8 / 73 / 927 ms, mixed (n/8) 8.4 / 68 / 848 ms
+    const bool want_rank = mode && strcmp(mode, "rank") == 0;
+    const bool want_blocked = blocked_ok && !want_rank && !(mode && strcmp(mode, "mixed") == 0);
     const bool want_mixed = blocked_ok && mode && strcmp(mode, "mixed") == 0;
     int t_dense = std::max(512, std::min(6144, p.n / 128));
     if (tmin && atoi(tmin) >= 512) t_dense = std::min(6144, atoi(tmin));
@@ -512,8 +518,8 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         const size_t smem = (((size_t)p.n + 127) & ~(size_t)127) * sizeof(T);  // padded to whole 128-column groups
         const double avgB = p.k ? (double)p.nnzB / (double)p.k : 0.0;
         const int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
-        TRY(set_smem(h, k_num_dense_cta<T>, smem));
-        k_num_dense_cta<T><<<persistent_grid(h, cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha);
+        TRY(set_smem(h, k_num_dense_cta<T, false>, smem));
+        k_num_dense_cta<T, false><<<persistent_grid(h, cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, SinglePassArgs{});
         return check_launch(h, "k_num_dense_cta");
       }
       // fp64 with n between the fp32 and fp64 budgets: column blocks
@@ -532,12 +538,21 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
           p.bounds_nblk = nblk;
           p.bounds_W = W;
         }
-        TRY(set_smem(h, k_num_dense_pieces<T, PIECES_NT>, smem));
+        // B200SP_WINDOW_TURN = windows per hand-off of the short-segment path (1, 4 or 8), B200SP_FLAT_BELOW =
+        // products per piece below which a chunk takes it (experiment switches; defaults measured on B200)
+        // (profiles/r02_heavy_modes_window_turns.jsonl: numeric pass at R-MAT scale 16 / 18 / 20 with 1, 4, 8 windows
+        // per turn 5.06 / 48.3 / 585, 4.67 / 48.4 / 624, 5.35 / 50.7 / 712 ms; raising FLAT_BELOW to 64 - 128 loses everywhere:
+        // the window path is bound by locating and loading its products, not by the hand-off)
+        int wpt = 1, flat_below = PIECES_FLAT_BELOW;
+        if (const char *e = getenv("B200SP_WINDOW_TURN")) wpt = atoi(e);
+        if (const char *e = getenv("B200SP_FLAT_BELOW")) flat_below = std::max(0, atoi(e));
+        auto kern = wpt >= 8 ? k_num_dense_pieces<T, PIECES_NT, 8> : wpt >= 4 ? k_num_dense_pieces<T, PIECES_NT, 4> : k_num_dense_pieces<T, PIECES_NT, 1>;
+        TRY(set_smem(h, kern, smem));
         int per_sm = 1;
-        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_dense_pieces<T, PIECES_NT>, PIECES_NT, smem));
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PIECES_NT, smem));
         const int grid = std::max(1, std::min(cnt, h->num_sms * std::max(1, per_sm)));
         CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, sizeof(int), st));  // rows are handed out by ticket
-        k_num_dense_pieces<T, PIECES_NT><<<grid, PIECES_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha);
+        kern<<<grid, PIECES_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, flat_below);
         return check_launch(h, "k_num_dense_pieces");
       }
       // B not canonical (or absurdly wide): the global-memory kernel takes any input
@@ -594,55 +609,67 @@ int run_numeric(b200sp_context *h, const void *alpha, const void *Ax, const void
 
 }  // namespace
 
-extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, int64_t n, int64_t nnzA,
-                                      int64_t nnzB, const int32_t *dAp, const int32_t *dAj,
-                                      const int32_t *dBp, const int32_t *dBj, int alg,
-                                      float chunk_fraction, int64_t *num_products, int64_t *nnzC,
-                                      int32_t *dCp) {
-  if (!h) return B200SP_ERR_INVALID;
+namespace {
+
+struct WsLayout {
+  size_t o_ub, o_rs, o_rn, o_ts, o_st, total;
+  int ntiles;
+};
+
+// plan workspace: counters | rowub | rows_sym | rows_num | scan tile sums | single-pass row status
+WsLayout ws_layout(int m) {
+  WsLayout L;
+  L.ntiles = (m + SCAN_TILE - 1) / SCAN_TILE;
+  L.o_ub = align_up(sizeof(Counters), 256);
+  L.o_rs = L.o_ub + align_up((size_t)m * 4, 256);
+  L.o_rn = L.o_rs + align_up((size_t)m * 4, 256);
+  L.o_ts = L.o_rn + align_up((size_t)m * 4, 256);
+  L.o_st = L.o_ts + align_up((size_t)L.ntiles * 8, 256);
+  L.total = L.o_st + (size_t)m * 8;
+  return L;
+}
+
+// Stage 1 of the structure pass: products per row, their total, the bound sum_i min(products_i, n)
+// of nnz(C), the symbolic bins, the canonical check of B.  Ends with host sync #1.
+int spgemm_stage1(b200sp_context *h, int64_t m, int64_t k, int64_t n, int64_t nnzA, int64_t nnzB,
+                  const int32_t *dAp, const int32_t *dAj, const int32_t *dBp, const int32_t *dBj, int alg,
+                  float chunk_fraction, int32_t *dCp) {
   Plan &p = h->plan;
   p.valid = false;
+  p.stage1 = false;
+  p.single_pass = false;
   if (m < 0 || k < 0 || n < 0 || nnzA < 0 || nnzB < 0 || m >= INT32_MAX || k >= INT32_MAX || n >= INT32_MAX ||
       nnzA > INT32_MAX || nnzB > INT32_MAX)
     return fail(h, B200SP_ERR_INVALID, "bad shape m=%lld k=%lld n=%lld nnzA=%lld nnzB=%lld", (long long)m,
                 (long long)k, (long long)n, (long long)nnzA, (long long)nnzB);
-  if (!dAp || !dBp || !dCp || !nnzC || (nnzA && !dAj) || (nnzB && !dBj))
+  if (!dAp || !dBp || !dCp || (nnzA && !dAj) || (nnzB && !dBj))
     return fail(h, B200SP_ERR_INVALID, "null pointer argument");
   const bool chunked = (alg == B200SP_ALG2 || alg == B200SP_ALG3);
   if (chunked && !(chunk_fraction > 0.f && chunk_fraction <= 1.f))
     return fail(h, B200SP_ERR_INVALID, "chunk_fraction must be in (0,1], got %f", chunk_fraction);
-  DeviceGuard guard(h->device);
   cudaStream_t st = h->stream;
   p.m = (int)m; p.k = (int)k; p.n = (int)n; p.nnzA = nnzA; p.nnzB = nnzB;
   p.Ap = dAp; p.Aj = dAj; p.Bp = dBp; p.Bj = dBj; p.Cp = dCp;
   p.alg = alg;
   p.num_chunks = chunked ? (int)std::min<double>(64.0, std::ceil(1.0 / (double)chunk_fraction - 1e-6)) : 1;
-  p.num_products = 0; p.nnzC = 0; p.max_row_products = 0;
+  p.num_products = 0; p.nnzC = 0; p.max_row_products = 0; p.nnz_bound = 0;
   p.bounds_nblk = p.bounds_W = 0;
   memset(p.sym_count, 0, sizeof p.sym_count);
   memset(p.num_count, 0, sizeof p.num_count);
   plan_bins(p);
   h->numeric_timed = false;
-  if (num_products) *num_products = 0;
-  *nnzC = 0;
   if (m == 0) {
     CUDA_TRY(h, cudaMemsetAsync(dCp, 0, sizeof(int), st));
-    p.valid = true;
+    p.stage1 = true;
     return B200SP_OK;
   }
-  // workspace: counters | rowub | rows_sym | rows_num | scan tile sums
-  const int ntiles = (p.m + SCAN_TILE - 1) / SCAN_TILE;
-  const size_t o_ub = align_up(sizeof(Counters), 256);
-  const size_t o_rs = o_ub + align_up((size_t)p.m * 4, 256);
-  const size_t o_rn = o_rs + align_up((size_t)p.m * 4, 256);
-  const size_t o_ts = o_rn + align_up((size_t)p.m * 4, 256);
-  TRY(ensure(h, h->ws, o_ts + (size_t)ntiles * 8));
+  const WsLayout L = ws_layout(p.m);
+  TRY(ensure(h, h->ws, L.total));
   char *base = (char *)h->ws.ptr;
   Counters *ctr = (Counters *)base;
-  int *rowub = (int *)(base + o_ub);
-  p.rows_sym = (int *)(base + o_rs);
-  p.rows_num = (int *)(base + o_rn);
-  long long *tile_sums = (long long *)(base + o_ts);
+  int *rowub = (int *)(base + L.o_ub);
+  p.rows_sym = (int *)(base + L.o_rs);
+  p.rows_num = (int *)(base + L.o_rn);
 
   cudaEventRecord(h->ev[0], st);
   CUDA_TRY(h, cudaMemsetAsync(ctr, 0, sizeof(Counters), st));
@@ -671,6 +698,7 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
   const int sgrid = std::max(1, std::min((p.m + 255) / 256, h->num_sms * 8));
   k_scatter_rows<false><<<sgrid, 256, 0, st>>>(p.m, rowub, p.sym_limits, ctr, p.rows_sym);
   TRY(check_launch(h, "k_scatter_rows<sym>"));
+  cudaEventRecord(h->ev[1], st);  // (re-recorded at the end of stage 2)
   // sync #1: product total + symbolic bin sizes
   CUDA_TRY(h, cudaMemcpyAsync(h->h_counters, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(h, cudaStreamSynchronize(st));
@@ -682,10 +710,27 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
                 "canonicalise it first (b200sp_csr_sum_duplicates / b200sp_csr_sort_indices)");
   p.num_products = (int64_t)h->h_counters->total_products;
   p.max_row_products = h->h_counters->max_row_products;
-  if (num_products) *num_products = p.num_products;
+  p.nnz_bound = (int64_t)h->h_counters->total_ub;
+  for (int b = 0; b < p.sym_limits.nbins; ++b) p.sym_count[b] = h->h_counters->sym_count[b];
+  p.b_canonical = true;
+  p.stage1 = true;
+  return B200SP_OK;
+}
+
+// Stage 2: exact row sizes per symbolic bin, scan to C.indptr, numeric bins.  Ends with host sync #2.
+int spgemm_stage2(b200sp_context *h, int64_t *nnzC) {
+  Plan &p = h->plan;
+  cudaStream_t st = h->stream;
+  int32_t *dCp = p.Cp;
+  const WsLayout L = ws_layout(p.m);
+  char *base = (char *)h->ws.ptr;
+  Counters *ctr = (Counters *)base;
+  long long *tile_sums = (long long *)(base + L.o_ts);
+  const int ntiles = L.ntiles;
+  const int sgrid = std::max(1, std::min((p.m + 255) / 256, h->num_sms * 8));
   int off = 0;
   for (int b = 0; b < p.sym_limits.nbins; ++b) {
-    const int cnt = p.sym_count[b] = h->h_counters->sym_count[b];
+    const int cnt = p.sym_count[b];
     if (cnt > 0) TRY(launch_symbolic_bin(h, b, p.rows_sym + off, cnt));
     off += cnt;
   }
@@ -714,12 +759,151 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
   CUDA_TRY(h, cudaStreamSynchronize(st));
   cudaEventElapsedTime(&h->ms_symbolic, h->ev[0], h->ev[1]);
   p.nnzC = (int64_t)h->h_counters->nnz_c;
-  p.b_canonical = true;  // verified before sync #1
   for (int b = 0; b < p.num_limits.nbins; ++b) p.num_count[b] = h->h_counters->num_count[b];
   *nnzC = p.nnzC;
   if (p.nnzC > INT32_MAX)
     return fail(h, B200SP_ERR_OVERFLOW, "nnz(C) = %lld does not fit the int32 indptr of CSR", (long long)p.nnzC);
+  p.single_pass = false;
   p.valid = true;
+  return B200SP_OK;
+}
+
+// The single-pass kernel pays one sweep of the n accumulator columns per row whatever the row
+// holds, and saves the structure pass (one more walk of the products): it wins where the rows of C
+// are well filled.  Measured on B200 (profiles/r02_single_pass_sweep.txt).
+bool single_pass_pays(const Plan &p, int dtype) {
+  const size_t s = dtype == B200SP_R_64F ? 8 : 4;
+  if (const char *e = getenv("B200SP_SINGLE_PASS")) {
+    if (strcmp(e, "0") == 0) return false;
+  }
+  if (p.m == 0 || p.num_chunks > 1 || (size_t)p.n * s > SMEM_DENSE_MAX || p.nnz_bound > INT32_MAX) return false;
+  // products per row, in units of n, from which the single pass is chosen.  Measured cross-over on B200
+  // (profiles/r02_single_pass_sweep_v17.jsonl): C3 16384^2 level at 0.15 (1.092 vs 1.105 ms), ahead from 0.41 on
+  // (d = 1e-2, 1.64: 1.625 -> 1.355 ms); C4 8192^2 ahead from 0.07 on (d = 1e-1, 82: 12.1 -> 8.35 ms)
+  double ratio = 0.25;
+  if (const char *e = getenv("B200SP_SINGLE_PASS_RATIO")) ratio = atof(e);
+  return (double)p.num_products >= ratio * (double)p.m * (double)p.n;
+}
+
+}  // namespace
+
+extern "C" int b200sp_spgemm_estimate(b200sp_handle_t h, int dtype, int64_t m, int64_t k, int64_t n, int64_t nnzA,
+                                      int64_t nnzB, const int32_t *dAp, const int32_t *dAj, const int32_t *dBp,
+                                      const int32_t *dBj, int alg, float chunk_fraction, int32_t *dCp,
+                                      int64_t *num_products, int64_t *nnz_bound, int *single_pass) {
+  if (!h) return B200SP_ERR_INVALID;
+  if (dtype != B200SP_R_32F && dtype != B200SP_R_64F) return fail(h, B200SP_ERR_INVALID, "unsupported dtype %d", dtype);
+  DeviceGuard guard(h->device);
+  if (num_products) *num_products = 0;
+  if (nnz_bound) *nnz_bound = 0;
+  if (single_pass) *single_pass = 0;
+  TRY(spgemm_stage1(h, m, k, n, nnzA, nnzB, dAp, dAj, dBp, dBj, alg, chunk_fraction, dCp));
+  Plan &p = h->plan;
+  p.single_pass = single_pass_pays(p, dtype);
+  if (num_products) *num_products = p.num_products;
+  if (nnz_bound) *nnz_bound = p.nnz_bound;
+  if (single_pass) *single_pass = p.single_pass ? 1 : 0;
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, int64_t n, int64_t nnzA,
+                                      int64_t nnzB, const int32_t *dAp, const int32_t *dAj,
+                                      const int32_t *dBp, const int32_t *dBj, int alg,
+                                      float chunk_fraction, int64_t *num_products, int64_t *nnzC,
+                                      int32_t *dCp) {
+  if (!h) return B200SP_ERR_INVALID;
+  if (!nnzC) return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  Plan &p = h->plan;
+  DeviceGuard guard(h->device);
+  const bool reuse = (alg & B200SP_ALG_REUSE_ESTIMATE) != 0;
+  alg &= ~B200SP_ALG_REUSE_ESTIMATE;
+  if (num_products) *num_products = 0;
+  *nnzC = 0;
+  if (reuse) {
+    if (!p.stage1 || p.m != m || p.k != k || p.n != n || p.nnzA != nnzA || p.nnzB != nnzB || p.Ap != dAp ||
+        p.Aj != dAj || p.Bp != dBp || p.Bj != dBj || p.Cp != dCp || p.alg != alg)
+      return fail(h, B200SP_ERR_STATE, "B200SP_ALG_REUSE_ESTIMATE without a matching b200sp_spgemm_estimate");
+  } else {
+    TRY(spgemm_stage1(h, m, k, n, nnzA, nnzB, dAp, dAj, dBp, dBj, alg, chunk_fraction, dCp));
+  }
+  p.stage1 = false;  // consumed
+  if (num_products) *num_products = p.num_products;
+  if (m == 0) {
+    p.valid = true;
+    return B200SP_OK;
+  }
+  return spgemm_stage2(h, nnzC);
+}
+
+namespace {
+
+template <typename T>
+int run_single_pass(b200sp_context *h, const void *alpha, const void *Ax, const void *Bx, int *Cj, void *Cx) {
+  Plan &p = h->plan;
+  const T a = alpha ? *(const T *)alpha : T(1);
+  cudaStream_t st = h->stream;
+  const WsLayout L = ws_layout(p.m);
+  char *base = (char *)h->ws.ptr;
+  Counters *ctr = (Counters *)base;
+  unsigned long long *status = (unsigned long long *)(base + L.o_st);
+  const size_t smem = (((size_t)p.n + 127) & ~(size_t)127) * sizeof(T);
+  const double avgB = p.k ? (double)p.nnzB / (double)p.k : 0.0;
+  const int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
+  TRY(set_smem(h, k_num_dense_cta<T, true>, smem));
+  int per_sm = 0;  // every CTA must be resident: rows wait for the rows before them
+  CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_dense_cta<T, true>, nt, smem));
+  if (per_sm < 1) return fail(h, B200SP_ERR_CUDA, "k_num_dense_cta<single pass> does not fit an SM");
+  const int grid = std::max(1, std::min(p.m, h->num_sms * per_sm));
+  CUDA_TRY(h, cudaMemsetAsync(status, 0, (size_t)p.m * 8, st));
+  CUDA_TRY(h, cudaMemsetAsync(&ctr->num_cursor[0], 0, sizeof(int), st));  // the row ticket
+  SinglePassArgs sp{&ctr->num_cursor[0], status, p.Cp, &ctr->nnz_c};
+  k_num_dense_cta<T, true><<<grid, nt, smem, st>>>(nullptr, p.m, p.n, p.Ap, p.Aj, (const T *)Ax, p.Bp, p.Bj, (const T *)Bx,
+                                                  (int)p.nnzB, nullptr, Cj, (T *)Cx, a, sp);
+  return check_launch(h, "k_num_dense_cta<single pass>");
+}
+
+}  // namespace
+
+extern "C" int b200sp_spgemm_single_pass(b200sp_handle_t h, int dtype, const void *alpha, const void *dAx,
+                                         const void *dBx, int32_t *dCj, void *dCx, int64_t capacity, int64_t *nnzC) {
+  if (!h) return B200SP_ERR_INVALID;
+  Plan &p = h->plan;
+  if (!p.stage1 || !p.single_pass)
+    return fail(h, B200SP_ERR_STATE, "spgemm_single_pass needs a b200sp_spgemm_estimate that returned single_pass = 1");
+  if (dtype != B200SP_R_32F && dtype != B200SP_R_64F) return fail(h, B200SP_ERR_INVALID, "unsupported dtype %d", dtype);
+  if (!nnzC) return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  if ((size_t)p.n * (dtype == B200SP_R_64F ? 8 : 4) > SMEM_DENSE_MAX)
+    return fail(h, B200SP_ERR_INVALID, "dtype differs from the one given to b200sp_spgemm_estimate");
+  if (capacity < p.nnz_bound)
+    return fail(h, B200SP_ERR_INVALID, "capacity %lld is below the bound %lld of nnz(C)", (long long)capacity,
+                (long long)p.nnz_bound);
+  *nnzC = 0;
+  DeviceGuard guard(h->device);
+  cudaStream_t st = h->stream;
+  p.stage1 = false;  // consumed
+  if (p.nnz_bound == 0) {  // no products at all: C is empty
+    CUDA_TRY(h, cudaMemsetAsync(p.Cp, 0, (size_t)(p.m + 1) * sizeof(int), st));
+    cudaEventElapsedTime(&h->ms_symbolic, h->ev[0], h->ev[1]);
+    h->ms_numeric = 0.f;
+    p.nnzC = 0;
+    p.valid = false;
+    return B200SP_OK;
+  }
+  if (!dAx || !dBx || !dCj || !dCx) return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  cudaEventRecord(h->ev[2], st);
+  int rc = dtype == B200SP_R_32F ? run_single_pass<float>(h, alpha, dAx, dBx, dCj, dCx)
+                                 : run_single_pass<double>(h, alpha, dAx, dBx, dCj, dCx);
+  cudaEventRecord(h->ev[3], st);
+  if (rc != B200SP_OK) return rc;
+  // the one other host synchronisation: nnz(C) (the reference's cusparseSpMatGetSize sync)
+  Counters *ctr = (Counters *)h->ws.ptr;
+  CUDA_TRY(h, cudaMemcpyAsync(&h->h_counters->nnz_c, &ctr->nnz_c, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(h, cudaStreamSynchronize(st));
+  cudaEventElapsedTime(&h->ms_symbolic, h->ev[0], h->ev[1]);
+  h->numeric_timed = true;
+  p.nnzC = (int64_t)h->h_counters->nnz_c;
+  *nnzC = p.nnzC;
+  p.valid = false;  // no row lists exist: a value-only re-run has to go through estimate again
   return B200SP_OK;
 }
 
@@ -808,9 +992,11 @@ int run_spmv(b200sp_context *h, int m, int n, int64_t nnz, int64_t ncols, const 
     return check_launch(h, "k_spmv_fixup");
   }
   const double avg = (double)nnz / (double)m;
-  // 128-bit loads pay once a row fills a few 4-entry lanes; on C2 (10.5 entries per row, unaligned
-  // row starts) half of every 16-byte load is masked and the scalar kernel is 8 % faster (66 vs 72 us)
-  if (vec && (force_vec4 || avg >= 16.0)) {  // four entries per lane and trip: a quarter of the lanes per row
+  // 128-bit loads pay only once a row fills all 32 lanes several times over: measured on B200 with
+  // 1.1e7 nonzeros (profiles/r02_spmv_sweep_v16.jsonl, us, 4-byte / 128-bit loads): 10.5 entries per row
+  // 67.6 / 74.6, 64: 60.3 / 66.4, 128: 51.2 / 55.3, 256: 45.1 / 38.9 (unaligned row starts mask half of
+  // every 16-byte load of a short row)
+  if (vec && (force_vec4 || avg >= 192.0)) {  // four entries per lane and trip: a quarter of the lanes per row
     const int G = avg <= 3 ? 1 : avg <= 6 ? 2 : avg <= 12 ? 4 : avg <= 24 ? 8 : avg <= 48 ? 16 : 32;
     const int gx = std::max(1, std::min((int)(((int64_t)m + 256 / G - 1) / (256 / G)), h->num_sms * 16));
     dim3 grid(gx, (unsigned)ncols);

@@ -561,16 +561,68 @@ __device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane,
   }
 }
 
-template <typename T>
+// ---- single-pass mode (SINGLE = true) ---------------------------------------------------------
+// The same kernel without a structure pass in front of it: rows are taken in row order from a
+// ticket counter, a row's output position is the number of entries of all earlier rows, obtained
+// with a decoupled look-back over per-row status words (the chained-scan protocol of single-pass
+// prefix sums: a row publishes its own count as soon as it knows it, then sums its predecessors'
+// counts back to the nearest published inclusive prefix), and the kernel writes C.indptr itself.
+// C.indices / C.data have room for an upper bound of nnz(C); the caller trims them afterwards.
+// Every CTA of the grid must be resident (the host sizes the grid from the occupancy query): a row
+// only ever waits for rows with smaller tickets, which are running or done.
+struct SinglePassArgs {
+  int *ticket;                  // zeroed before the launch
+  unsigned long long *status;   // m words, zeroed before the launch: flag << 62 | value
+  int *Cp;                      // m + 1 row pointers, written here
+  unsigned long long *nnz_out;  // total, written by the last row
+};
+#define SP_FLAG_AGG (1ull << 62)
+#define SP_FLAG_PREFIX (2ull << 62)
+#define SP_VALUE_MASK ((1ull << 62) - 1)
+
+// Warp-wide: publishes `own` for `row` and returns the number of entries of rows [0, row).
+__device__ __forceinline__ long long single_pass_lookback(volatile unsigned long long *status, int row, long long own, int lane) {
+  if (row == 0) {
+    if (lane == 0) status[0] = SP_FLAG_PREFIX | (unsigned long long)own;
+    return 0;
+  }
+  if (lane == 0) status[row] = SP_FLAG_AGG | (unsigned long long)own;
+  long long excl = 0;
+  for (int j = row - 1;; j -= 32) {  // lane l looks at row j - l (rows before 0 count as prefix 0)
+    const int idx = j - lane;
+    unsigned long long s;
+    int fp;
+    for (;;) {
+      s = idx >= 0 ? status[idx] : SP_FLAG_PREFIX;
+      const unsigned flag = (unsigned)(s >> 62);
+      const unsigned pref = __ballot_sync(FULL, flag == 2u), inval = __ballot_sync(FULL, flag == 0u);
+      fp = pref ? __ffs(pref) - 1 : 32;  // nearest predecessor with an inclusive prefix
+      const unsigned upto = fp < 32 ? (2u << fp) - 1u : FULL;
+      if ((inval & upto) == 0) break;
+      __nanosleep(40);
+    }
+    long long v = lane <= fp ? (long long)(s & SP_VALUE_MASK) : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    excl += v;
+    if (fp < 32) break;
+  }
+  if (lane == 0) status[row] = SP_FLAG_PREFIX | (unsigned long long)(excl + own);
+  return excl;
+}
+
+template <typename T, bool SINGLE>
 __global__ void __launch_bounds__(DENSE_MAX_NT, 3)
 k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
                 const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
                 const int *__restrict__ Bj, const T *__restrict__ Bx, int nnzB, const int *__restrict__ Cp,
-                int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
+                int *__restrict__ Cj, T *__restrict__ Cx, T alpha, SinglePassArgs sp) {
   extern __shared__ __align__(16) unsigned char smem_raw[];  // round_up(n, 128) accumulator columns
   __shared__ DenseSeg<T> s_seg[DENSE_CAP + DENSE_PAD];       // the staged pieces of the round
   __shared__ int s_wcnt[DENSE_MAX_NT / 32];
   __shared__ int s_scan[DENSE_MAX_NT / 32];
+  __shared__ int s_row;
+  __shared__ long long s_pos;
   T *acc = reinterpret_cast<T *>(smem_raw);
   const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
   const T UNT = NegZero<T>::value();
@@ -581,8 +633,21 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
   const int c_lo = min(w * cpw, npad), c_hi = min(c_lo + cpw, npad);
   __syncthreads();
 
-  for (int ridx = blockIdx.x; ridx < nrows; ridx += gridDim.x) {
-    const int row = rows[ridx];
+  for (int ridx = blockIdx.x;; ridx += gridDim.x) {
+    int row;
+    if (SINGLE) {
+      // The ticket is drawn when the CTA is free, not ahead of time: a row waits for every row before it, so
+      // tickets must go out in the order in which CTAs come free.  Measured on C3 (kernel time): drawn here
+      // 1.22 ms; drawn a row ahead 1.98 ms (a late CTA sits on a low ticket and all rows behind it spin);
+      // drawn before the count pass 1.36 ms.
+      if (tid == 0) s_row = atomicAdd(sp.ticket, 1);
+      __syncthreads();  // the previous read of s_row lies before the barriers of the row body
+      row = s_row;
+      if (row >= nrows) break;
+    } else {
+      if (ridx >= nrows) break;
+      row = rows[ridx];
+    }
     const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
     for (int base = a_begin; base < a_end; base += NT) {
       // ---- stage: thread t takes A nonzero base+t; its B row is cut into pieces of <= NT
@@ -635,14 +700,34 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
       if (total == 0) __syncthreads();  // s_scan is rewritten by the next chunk
     }
     // ---- output: warp w owns columns [c_lo, c_hi); count, prefix over the warps, ordered emit ----
-    const int mine = dense_count<T>(acc, c_lo, c_hi, lane);
+    const int mine = a_begin < a_end ? dense_count<T>(acc, c_lo, c_hi, lane) : 0;
     if (lane == 0) s_wcnt[w] = mine;
     __syncthreads();
-    int pos = __ldg(Cp + row);
+    int pos, row_nnz;
+    if (SINGLE) {
+      row_nnz = 0;
+      for (int q = 0; q < nw; ++q) row_nnz += s_wcnt[q];
+      if (w == 0) {
+        const long long excl = single_pass_lookback(sp.status, row, row_nnz, lane);
+        if (lane == 0) {
+          s_pos = excl;
+          sp.Cp[row] = (int)excl;
+          if (row == nrows - 1) {
+            sp.Cp[nrows] = (int)(excl + row_nnz);
+            *sp.nnz_out = (unsigned long long)(excl + row_nnz);
+          }
+        }
+      }
+      __syncthreads();
+      pos = (int)s_pos;
+      if (row_nnz == 0) continue;  // CTA-uniform; the next ticket's barrier orders the reuse of s_pos / s_wcnt
+    } else {
+      pos = __ldg(Cp + row);
+      row_nnz = __ldg(Cp + row + 1) - pos;
+    }
     for (int q = 0; q < w; ++q) pos += s_wcnt[q];
     // well-filled rows: 32 columns per step with fully coalesced stores; sparse rows: 128 columns
     // per step (a quarter of the instructions, stores strided by the fill)
-    const int row_nnz = __ldg(Cp + row + 1) - __ldg(Cp + row);
     if (row_nnz > (npad >> 2)) {
       if (alpha == T(1)) dense_emit_ballot<T, false>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
       else dense_emit_ballot<T, true>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
@@ -795,12 +880,12 @@ __device__ __forceinline__ void window_apply(T *__restrict__ acc, unsigned *__re
 // 16/18 unchanged, scale 20 961 -> 827 ms, scale 22 16.3 -> 12.0 s; 64 and above lose at scale 16-18).
 constexpr int PIECES_FLAT_BELOW = 32;
 
-template <typename T, int NT>
+template <typename T, int NT, int WPT>
 __global__ void __launch_bounds__(NT, 1)
 k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ticket, int n, int W, int nblk,
                    const int *__restrict__ Ap, const int *__restrict__ Aj, const T *__restrict__ Ax,
                    const int *__restrict__ bounds, const int *__restrict__ Bj, const T *__restrict__ Bx,
-                   int nnzB, const int *__restrict__ Cp, int *__restrict__ Cj, T *__restrict__ Cx, T alpha) {
+                   int nnzB, const int *__restrict__ Cp, int *__restrict__ Cj, T *__restrict__ Cx, T alpha, int flat_below) {
   constexpr int NW = NT / 32, CAP = 2 * NT;
   extern __shared__ __align__(16) unsigned char smem_raw[];  // W accumulators, then W/32 bitmap words
   __shared__ DenseSeg<T> s_seg[CAP + BLOCKED_PAD];
@@ -818,7 +903,7 @@ k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ti
   unsigned *bm = reinterpret_cast<unsigned *>(smem_raw + (size_t)W * sizeof(T));
   const int tid = threadIdx.x, lane = lane_id(), w = tid >> 5;
   if (tid < NW) mbar_init(&s_turn[tid], 1);
-  int gwin = 0;   // windows handed out so far (CTA-uniform): window g belongs to warp g % NW
+  int gwin = 0;   // turns (groups of WPT windows) handed out so far (CTA-uniform): turn g belongs to warp g % NW
   int turns = 0;  // hand-offs this warp has consumed (phase of its barrier)
   const int nwords = W >> 5;  // W is a multiple of 128
   const T UNT = NegZero<T>::value();
@@ -876,7 +961,7 @@ k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ti
           if (q < w) off += v, poff += vp;
           total += v, P += vp;
         }
-        if (total > 0 && P < PIECES_FLAT_BELOW * total) {
+        if (total > 0 && P < flat_below * total) {
           // ---- window path: short segments.  The chunk's products form one stream (A order);
           //      window i = products [32 i, 32 i + 32) is applied by ONE warp, same-column lanes
           //      chained in lane order; the windows are applied strictly one after the other
@@ -888,45 +973,67 @@ k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ti
           f_a[tid] = av;
           if (tid == 0) f_pre[NT] = P;
           __syncthreads();
+          // a TURN = WPT consecutive windows applied by one warp: the hand-off (~420 cycles) is paid
+          // once per turn, the windows inside a turn follow each other in program order
           const int nwin = (P + 31) >> 5;
-          int i = (w - gwin) & (NW - 1);  // my first window of this chunk
-          int col = 0;
-          T prod = T(0);
-          bool act = false;
-          auto fetch = [&](int win) {
-            const int pp = (win << 5) + lane;
-            act = win < nwin && pp < P;
-            if (act) {
-              int lo = 0, hi = NT;  // largest q with f_pre[q] <= pp
+          const int nturn = (nwin + WPT - 1) / WPT;
+          int i = (w - gwin) & (NW - 1);  // my first turn of this chunk
+          int col[WPT];
+          T prod[WPT];
+          unsigned actm = 0;  // bit u: my lane holds a product in window u of the turn
+          auto fetch = [&](int turn) {
+            actm = 0;
 #pragma unroll
-              for (int st = 0; st < 8; ++st) {
-                const int mid = (lo + hi) >> 1;
-                if (f_pre[mid] <= pp) lo = mid;
-                else hi = mid;
+            for (int u = 0; u < WPT; ++u) {
+              const int pp = ((turn * WPT + u) << 5) + lane;
+              col[u] = 0;
+              prod[u] = T(0);
+              if (turn < nturn && pp < P) {
+                actm |= 1u << u;
+                int lo = 0, hi = NT;  // largest q with f_pre[q] <= pp
+#pragma unroll
+                for (int st = 0; st < 8; ++st) {
+                  const int mid = (lo + hi) >> 1;
+                  if (f_pre[mid] <= pp) lo = mid;
+                  else hi = mid;
+                }
+                const int idx = f_sbase[lo] + pp;
+                col[u] = __ldg(Bj + idx) - c0;
+                prod[u] = add_rn(mul_rn(f_a[lo], __ldg(Bx + idx)), T(0));  // -0.0 -> +0.0
               }
-              const int idx = f_sbase[lo] + pp;
-              col = __ldg(Bj + idx) - c0;
-              prod = add_rn(mul_rn(f_a[lo], __ldg(Bx + idx)), T(0));  // -0.0 -> +0.0
             }
           };
           fetch(i);
-          for (; i < nwin; i += NW) {
-            const int mycol = col;
-            const T myprod = prod;
-            const bool myact = act;
-            fetch(i + NW);  // the next window of this warp is located and requested before the wait
-            const unsigned peers = __match_any_sync(FULL, myact ? mycol : (-1 - lane));
-            const bool any_multi = __any_sync(FULL, myact && (peers & (peers - 1)));
-            const int maxn = any_multi ? __reduce_max_sync(FULL, __popc(peers)) : 1;
-            if (gwin + i > 0) {  // every window but the very first of the CTA waits for its predecessor
+          for (; i < nturn; i += NW) {
+            int mycol[WPT];
+            T myprod[WPT];
+            const unsigned myact = actm;
+#pragma unroll
+            for (int u = 0; u < WPT; ++u) mycol[u] = col[u], myprod[u] = prod[u];
+            fetch(i + NW);  // the next turn of this warp is located and requested before the wait
+            unsigned peers[WPT];
+            int maxn[WPT];
+#pragma unroll
+            for (int u = 0; u < WPT; ++u) {
+              const bool a = (myact >> u) & 1u;
+              peers[u] = __match_any_sync(FULL, a ? mycol[u] : (-1 - lane));
+              const bool any_multi = __any_sync(FULL, a && (peers[u] & (peers[u] - 1)));
+              maxn[u] = any_multi ? __reduce_max_sync(FULL, __popc(peers[u])) : 1;
+            }
+            if (gwin + i > 0) {  // every turn but the very first of the CTA waits for its predecessor
               mbar_wait(&s_turn[w], turns & 1);
               ++turns;
             }
-            window_apply<T>(acc, bm, mycol, myact, myprod, peers, any_multi, maxn);
-            __syncwarp();
+#pragma unroll
+            for (int u = 0; u < WPT; ++u) {
+              if ((u << 5) < P - ((i * WPT) << 5)) {  // warp-uniform: window u of this turn exists
+                window_apply<T>(acc, bm, mycol[u], (myact >> u) & 1u, myprod[u], peers[u], maxn[u] > 1, maxn[u]);
+                __syncwarp();
+              }
+            }
             if (lane == 0) mbar_arrive(&s_turn[(w + 1) & (NW - 1)]);
           }
-          gwin += nwin;
+          gwin += nturn;
           __syncthreads();
           continue;
         }

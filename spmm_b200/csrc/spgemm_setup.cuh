@@ -34,6 +34,7 @@ struct Counters {
   int sym_cursor[MAX_BINS];
   int num_count[MAX_BINS];
   int num_cursor[MAX_BINS];
+  unsigned long long total_ub;  // sum_i min(products_i, n): an upper bound of nnz(C) (single-pass mode)
 };
 
 // prods[i] = sum over the nonzeros (i,k) of A of nnz(B_k); ub[i] = min(prods[i], n) is the
@@ -46,17 +47,18 @@ k_row_products(int m, int n, const int *__restrict__ Ap, const int *__restrict__
                const int *__restrict__ Bp, int *__restrict__ rowub, int *__restrict__ Cp,
                BinLimits bl, Counters *ctr) {
   __shared__ int s_hist[MAX_BINS];
-  __shared__ unsigned long long s_total;
+  __shared__ unsigned long long s_total, s_ub;
   __shared__ int s_max;
   if (threadIdx.x < MAX_BINS) s_hist[threadIdx.x] = 0;
   if (threadIdx.x == 0) {
     s_total = 0;
+    s_ub = 0;
     s_max = 0;
   }
   __syncthreads();
   const int sub = threadIdx.x & (G - 1);
   const int groups_per_block = 256 / G;
-  long long my_total = 0;
+  long long my_total = 0, my_ub = 0;
   int my_max = 0;
   for (int row0 = blockIdx.x * groups_per_block; row0 < m; row0 += gridDim.x * groups_per_block) {
     const int row = row0 + threadIdx.x / G;
@@ -84,19 +86,23 @@ k_row_products(int m, int n, const int *__restrict__ Ap, const int *__restrict__
         atomicAdd(&s_hist[classify(bl, ub)], 1);
       }
       my_total += s;
+      my_ub += ub;
       my_max = max(my_max, p);
     }
   }
   my_total = warp_sum(my_total);
+  my_ub = warp_sum(my_ub);
   my_max = __reduce_max_sync(FULL, my_max);
   if (lane_id() == 0) {
     atomicAdd(&s_total, (unsigned long long)my_total);
+    atomicAdd(&s_ub, (unsigned long long)my_ub);
     atomicMax(&s_max, my_max);
   }
   __syncthreads();
   if (threadIdx.x < bl.nbins && s_hist[threadIdx.x]) atomicAdd(&ctr->sym_count[threadIdx.x], s_hist[threadIdx.x]);
   if (threadIdx.x == 0) {
     if (s_total) atomicAdd(&ctr->total_products, s_total);
+    if (s_ub) atomicAdd(&ctr->total_ub, s_ub);
     if (s_max) atomicMax(&ctr->max_row_products, s_max);
   }
 }

@@ -52,7 +52,7 @@ class SpgemmPlan:
     thread's handle, which keeps ONE plan: pass a private handle (`_lib.new_handle`) to keep
     several plans alive."""
 
-    def __init__(self, a, b, alg=0, chunk_fraction=0.2, handle=None):
+    def __init__(self, a, b, alg=0, chunk_fraction=0.2, handle=None, _estimate=None):
         m, k = a.shape
         _, n = b.shape
         self.a, self.b = _cast_common_type(a, b)
@@ -62,7 +62,11 @@ class SpgemmPlan:
         lib = _lib.load()
         self.h = handle if handle is not None else _lib.handle(dev.index)
         _bind_stream(self.h, dev)
-        self.indptr = torch.empty(m + 1, dtype=torch.int32, device=dev)  # cusparse.py:2039
+        if _estimate is not None:  # spgemm() has just run b200sp_spgemm_estimate on these operands and this handle
+            self.indptr = _estimate
+            alg = int(alg) | _lib.ALG_REUSE_ESTIMATE
+        else:
+            self.indptr = torch.empty(m + 1, dtype=torch.int32, device=dev)  # cusparse.py:2039
         prods, c_nnz = ctypes.c_int64(0), ctypes.c_int64(0)
         _lib.check(self.h, lib.b200sp_spgemm_symbolic(
             self.h, m, k, n, self.a.nnz, self.b.nnz, self.a.indptr.data_ptr(), self.a.indices.data_ptr(),
@@ -93,6 +97,39 @@ class SpgemmPlan:
         return c
 
 
+def _spgemm_single_pass(a, b, alpha):
+    """b200sp_spgemm_estimate, then b200sp_spgemm_single_pass when the library chooses it.
+    Returns the product, or (a, b, indptr) for the two-pass plan to continue from the estimate."""
+    m, k = a.shape
+    _, n = b.shape
+    a, b = _cast_common_type(a, b)
+    dev, dt = a.device, a.dtype
+    lib = _lib.load()
+    h = _lib.handle(dev.index)
+    _bind_stream(h, dev)
+    indptr = torch.empty(m + 1, dtype=torch.int32, device=dev)  # cusparse.py:2039
+    prods, bound, single = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int(0)
+    _lib.check(h, lib.b200sp_spgemm_estimate(
+        h, _dt_code(dt), m, k, n, a.nnz, b.nnz, a.indptr.data_ptr(), a.indices.data_ptr(), b.indptr.data_ptr(),
+        b.indices.data_ptr(), 0, 0.2, indptr.data_ptr(), ctypes.byref(prods), ctypes.byref(bound), ctypes.byref(single)))
+    if not single.value:
+        return a, b, indptr
+    cap = int(bound.value)
+    try:
+        c_indices = torch.empty(cap, dtype=torch.int32, device=dev)
+        c_data = torch.empty(cap, dtype=_TORCH_DT[dt], device=dev)
+    except torch.OutOfMemoryError as e:  # same except clause as the reference's callers
+        raise MemoryError(str(e)) from e
+    _abuf, aptr = _scalar(alpha, dt)
+    c_nnz = ctypes.c_int64(0)
+    _lib.check(h, lib.b200sp_spgemm_single_pass(h, _dt_code(dt), aptr, a.data.data_ptr(), b.data.data_ptr(),
+                                                c_indices.data_ptr(), c_data.data_ptr(), cap, ctypes.byref(c_nnz)))
+    nnz = int(c_nnz.value)
+    c = csr_matrix((c_data[:nnz], c_indices[:nnz], indptr), shape=(m, n))
+    c._canonical = True
+    return c
+
+
 def spgemm(a, b, alpha=1, alg=0, chunk_fraction=0.2, verbose=False):
     """C = alpha * A * B for CSR matrices (reference: cusparse.py:2007-2142).
 
@@ -118,7 +155,16 @@ def spgemm(a, b, alpha=1, alg=0, chunk_fraction=0.2, verbose=False):
         raise ValueError(f"chunk_fraction must be in (0,1], got {chunk_fraction}")
     elif verbose:
         print("USING ALG3 or ALG2")
-    plan = SpgemmPlan(a, b, alg=alg, chunk_fraction=chunk_fraction)
+    est = None
+    if alg == 0:
+        # default mode: products per row first; well-filled C takes the single-pass kernel (C.indices /
+        # C.data allocated at the bound sum_i min(products_i, n), trimmed to views of nnz(C) entries -
+        # the memory-for-time trade of cuSPARSE's ALG1); anything else continues with the two-pass plan
+        c = _spgemm_single_pass(a, b, alpha)
+        if isinstance(c, csr_matrix):
+            return c
+        a, b, est = c
+    plan = SpgemmPlan(a, b, alg=alg, chunk_fraction=chunk_fraction, _estimate=est)
     if verbose:
         s = _lib.stats(plan.device.index)
         print("workspace GB =", s.workspace_bytes / (1024 ** 3), "products =", plan.num_products)

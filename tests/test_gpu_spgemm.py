@@ -191,6 +191,20 @@ def test_heavy_row_kernels_all_modes(b200, dtype, mode, acc_kb, tmin, monkeypatc
         assert_csr_bitwise(dev_spgemm(b200, A, B, alpha=0.5), oracle_spgemm(A, B, alpha=0.5), f"{name} {mode} alpha")
 
 
+@pytest.mark.parametrize("turn,flat", [("1", None), ("8", None), ("4", "128"), ("8", "4096")])
+def test_blocked_kernel_window_turns(b200, turn, flat, monkeypatch):
+    """The short-segment path of k_num_dense_pieces with 1 / 4 / 8 windows per hand-off turn and with
+    chunks of long segments forced onto it (B200SP_FLAT_BELOW): same bits whatever the schedule."""
+    monkeypatch.setenv("B200SP_HEAVY", "blocked")
+    monkeypatch.setenv("B200SP_WINDOW_TURN", turn)
+    if flat:
+        monkeypatch.setenv("B200SP_FLAT_BELOW", flat)
+    for name, (A, B) in {"hubs": helpers.hub_pair(), "skewed": helpers.skewed_pair()}.items():
+        assert_csr_bitwise(dev_spgemm(b200, A, B), oracle_spgemm(A, B), f"{name} turn={turn} flat={flat}")
+    A, B = helpers.hub_pair(dtype=np.float64, seed=4)
+    assert_csr_bitwise(dev_spgemm(b200, A, B), oracle_spgemm(A, B), f"hubs fp64 turn={turn} flat={flat}")
+
+
 def test_rmat16_bitwise(b200):
     """R-MAT scale 16 A @ A (4.0e8 products, nnz(C) 1.6e8, n = 65 536 > one accumulator): the C5
     recipe at the largest scale the oracle finishes in seconds."""
@@ -292,9 +306,10 @@ def test_numeric_reuse_new_values(b200):
     from spmm_b200 import _lib
     A, B = helpers.grid_case(128, 0.1)
     a, b = b200.csr_matrix(A), b200.csr_matrix(B)
-    c = b200.cusparse.spgemm(a, b)
+    plan = b200.cusparse.SpgemmPlan(a, b)  # the two-pass plan (spgemm() may take the single pass, which keeps none)
+    c = plan.numeric()
     a2 = b200.csr_matrix((a.data * 3.0, a.indices, a.indptr), shape=a.shape)
-    h = _lib.handle(0)
+    h = plan.h
     cx = torch.empty_like(c.data)
     cj = torch.empty_like(c.indices)
     _lib.check(h, _lib.load().b200sp_spgemm_numeric(h, _lib.R_32F, None, a2.data.data_ptr(), b.data.data_ptr(),

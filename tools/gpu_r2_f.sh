@@ -1,0 +1,13 @@
+#!/bin/bash
+# round 2, GPU call F: single-pass SpGEMM with ticket prefetch: tests, whole suite, bench line, launch list, ncu --set full
+mkdir -p gpurun_out
+( timeout 900 python -m pytest tests/test_gpu_single_pass.py -m gpu -x -q ) > gpurun_out/f_pytest_single.txt 2>&1
+echo "pytest rc=$?" >> gpurun_out/f_pytest_single.txt
+( time timeout 1800 python -m pytest tests -m gpu -x -q ) > gpurun_out/f_pytest.txt 2>&1
+echo "pytest rc=$?" >> gpurun_out/f_pytest.txt
+( time timeout 900 python bench.py ) > gpurun_out/f_bench_n1.json 2> gpurun_out/f_bench_n1.err
+echo "bench rc=$?" >> gpurun_out/f_bench_n1.err
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/f_launches.csv \
+   python bench.py --steps 2 --warmup 1 --no-cpu --no-extra --no-c5 > gpurun_out/f_ncu_launches.log 2>&1
+REPS=3 timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k_num_dense_cta" -s 2 -c 1 \
+   -o gpurun_out/f_ncu_c3 -f python tools/profile_cases.py c3_1e-2 > gpurun_out/f_ncu_c3.log 2>&1

@@ -29,8 +29,16 @@ CONFIGS = {
     "rank96_t2048": {"B200SP_HEAVY": "rank", "B200SP_RANK_ACC_KB": "96", "B200SP_HEAVY_MIN": "2048"},
     "mixed8": {"B200SP_HEAVY": "mixed", "B200SP_RANK_ACC_KB": "96", "B200SP_HEAVY_DENSE_DIV": "8"},
     "mixed4": {"B200SP_HEAVY": "mixed", "B200SP_RANK_ACC_KB": "96", "B200SP_HEAVY_DENSE_DIV": "4"},
+    # short-segment (window) path of the blocked kernel: windows per hand-off turn, products per piece below which it is taken
+    "blocked_w1": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "1"},
+    "blocked_w4": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "4"},
+    "blocked_w8": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "8"},
+    "blocked_w4_f64": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "4", "B200SP_FLAT_BELOW": "64"},
+    "blocked_w8_f64": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "8", "B200SP_FLAT_BELOW": "64"},
+    "blocked_w8_f96": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "8", "B200SP_FLAT_BELOW": "96"},
+    "blocked_w8_f128": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "8", "B200SP_FLAT_BELOW": "128"},
 }
-KEYS = ("B200SP_HEAVY", "B200SP_RANK_ACC_KB", "B200SP_HEAVY_MIN", "B200SP_HEAVY_DENSE_DIV")
+KEYS = ("B200SP_HEAVY", "B200SP_RANK_ACC_KB", "B200SP_HEAVY_MIN", "B200SP_HEAVY_DENSE_DIV", "B200SP_WINDOW_TURN", "B200SP_FLAT_BELOW")
 
 
 def run_once(A, b, rp, dev):
