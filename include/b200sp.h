@@ -197,6 +197,15 @@ int b200sp_host_unregister(void *ptr);
 int b200sp_memcpy_async(b200sp_handle_t handle, void *dst, const void *src, size_t bytes, int kind,
                         void *cuda_stream);
 
+/* Host only (no device is touched): out[i] = sum over the nonzeros (i, c) of A of nnz(B_c), the
+ * intermediate products of row i of A @ B, from host arrays - what the row-panel driver balances its
+ * panels by before anything is uploaded (the device-side count is part of b200sp_spgemm_symbolic /
+ * _estimate; cusparseSpGEMM_getNumProducts, spgemm_from_txt_alg3.cu:190-191, only gives the total).
+ * One multithreaded pass (nthreads <= 0: up to 16).  B200SP_ERR_INVALID for a malformed hAp or a
+ * column index outside [0, k). */
+int b200sp_host_row_products(int64_t m, int64_t k, const int32_t *hAp, const int32_t *hAj,
+                             const int32_t *hBp, int64_t *out, int nthreads);
+
 /* ------------------------------------------------------------ SpMV / SpMM ---- */
 
 /*

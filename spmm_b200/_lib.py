@@ -59,6 +59,7 @@ SYMBOLS = [
     ("b200sp_host_register", ctypes.c_int, [c_vp, ctypes.c_size_t]),
     ("b200sp_host_unregister", ctypes.c_int, [c_vp]),
     ("b200sp_memcpy_async", ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_size_t, ctypes.c_int, c_vp]),
+    ("b200sp_host_row_products", ctypes.c_int, [c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, ctypes.c_int]),
     ("b200sp_spmv", ctypes.c_int, [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     ("b200sp_spmv_noalloc", ctypes.c_int, [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     ("b200sp_spmm", ctypes.c_int,

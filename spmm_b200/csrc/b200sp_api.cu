@@ -104,6 +104,9 @@ struct b200sp_context {
   int spmv_key_m = -1;
   int64_t spmv_key_nnz = -1;
   int spmv_max_row = 0;
+  // launch geometry of the single-pass kernel, cached per (value size, CTA size, shared memory)
+  int sp_key_t = 0, sp_key_nt = 0, sp_per_sm = 0;
+  size_t sp_key_smem = 0;
   std::string err;
 };
 
@@ -525,7 +528,15 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       // fp64 with n between the fp32 and fp64 budgets: column blocks
     case NUM_DENSE_BLOCKED:
       if (p.b_canonical && (size_t)p.n * sizeof(T) <= (size_t)DENSE_BLOCKED_MAX_BLOCKS * SMEM_BLOCKED_MAX) {
-        const size_t budget = SMEM_BLOCKED_MAX;  // two CTAs of 256 threads per SM
+        // two CTAs of 256 threads per SM; B200SP_BLOCKED_KB / B200SP_BLOCKED_NT = experiment switches (accumulator
+        // kilobytes per CTA, 128 or 256 threads per CTA)
+        size_t budget = SMEM_BLOCKED_MAX;
+        int nt = PIECES_NT;
+        if (const char *e = getenv("B200SP_BLOCKED_KB")) {
+          const long v = atol(e);
+          if (v >= 8 && v <= 200) budget = (size_t)v * 1024;
+        }
+        if (const char *e = getenv("B200SP_BLOCKED_NT")) nt = atoi(e) == 128 ? 128 : PIECES_NT;
         const int nblk = (int)(((size_t)p.n * sizeof(T) + budget - 1) / budget);
         const int W = (((p.n + nblk - 1) / nblk) + 127) & ~127;  // whole 128-column groups
         const size_t smem = (size_t)W * sizeof(T) + (size_t)(W / 32) * 4;  // accumulators + touched-column bitmap
@@ -546,13 +557,14 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         int wpt = 1, flat_below = PIECES_FLAT_BELOW;
         if (const char *e = getenv("B200SP_WINDOW_TURN")) wpt = atoi(e);
         if (const char *e = getenv("B200SP_FLAT_BELOW")) flat_below = std::max(0, atoi(e));
-        auto kern = wpt >= 8 ? k_num_dense_pieces<T, PIECES_NT, 8> : wpt >= 4 ? k_num_dense_pieces<T, PIECES_NT, 4> : k_num_dense_pieces<T, PIECES_NT, 1>;
+        auto kern = nt == 128 ? k_num_dense_pieces<T, 128, 1>
+                    : wpt >= 8 ? k_num_dense_pieces<T, PIECES_NT, 8> : wpt >= 4 ? k_num_dense_pieces<T, PIECES_NT, 4> : k_num_dense_pieces<T, PIECES_NT, 1>;
         TRY(set_smem(h, kern, smem));
         int per_sm = 1;
-        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PIECES_NT, smem));
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt, smem));
         const int grid = std::max(1, std::min(cnt, h->num_sms * std::max(1, per_sm)));
         CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, sizeof(int), st));  // rows are handed out by ticket
-        kern<<<grid, PIECES_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, flat_below);
+        kern<<<grid, nt, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, flat_below);
         return check_launch(h, "k_num_dense_pieces");
       }
       // B not canonical (or absurdly wide): the global-memory kernel takes any input
@@ -849,11 +861,17 @@ int run_single_pass(b200sp_context *h, const void *alpha, const void *Ax, const 
   const size_t smem = (((size_t)p.n + 127) & ~(size_t)127) * sizeof(T);
   const double avgB = p.k ? (double)p.nnzB / (double)p.k : 0.0;
   const int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
-  TRY(set_smem(h, k_num_dense_cta<T, true>, smem));
-  int per_sm = 0;  // every CTA must be resident: rows wait for the rows before them
-  CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_dense_cta<T, true>, nt, smem));
-  if (per_sm < 1) return fail(h, B200SP_ERR_CUDA, "k_num_dense_cta<single pass> does not fit an SM");
-  const int grid = std::max(1, std::min(p.m, h->num_sms * per_sm));
+  // every CTA must be resident: rows wait for the rows before them.  The attribute call and the occupancy
+  // query cost ~10 us of host time between the estimate and the launch: done once per (type, shape) and handle
+  const int key_t = (int)sizeof(T);
+  if (h->sp_key_t != key_t || h->sp_key_nt != nt || h->sp_key_smem != smem) {
+    TRY(set_smem(h, k_num_dense_cta<T, true>, smem));
+    int per_sm = 0;
+    CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_dense_cta<T, true>, nt, smem));
+    if (per_sm < 1) return fail(h, B200SP_ERR_CUDA, "k_num_dense_cta<single pass> does not fit an SM");
+    h->sp_key_t = key_t; h->sp_key_nt = nt; h->sp_key_smem = smem; h->sp_per_sm = per_sm;
+  }
+  const int grid = std::max(1, std::min(p.m, h->num_sms * h->sp_per_sm));
   CUDA_TRY(h, cudaMemsetAsync(status, 0, (size_t)p.m * 8, st));
   CUDA_TRY(h, cudaMemsetAsync(&ctr->num_cursor[0], 0, sizeof(int), st));  // the row ticket
   SinglePassArgs sp{&ctr->num_cursor[0], status, p.Cp, &ctr->nnz_c};
@@ -1165,6 +1183,11 @@ extern "C" int b200sp_csr_is_canonical(b200sp_handle_t h, int64_t m, int64_t nco
   return B200SP_OK;
 }
 
+namespace {
+template <typename T>
+int run_sort_indices_stable(b200sp_context *h, int64_t m, int64_t nnz, const int *Ap, int *Aj, T *Ax);  // convert_api.inl
+}
+
 extern "C" int b200sp_csr_sort_indices(b200sp_handle_t h, int dtype, int64_t m, int64_t nnz, const int32_t *dAp,
                                        int32_t *dAj, void *dAx) {
   if (!h) return B200SP_ERR_INVALID;
@@ -1190,8 +1213,10 @@ extern "C" int b200sp_csr_sort_indices(b200sp_handle_t h, int dtype, int64_t m, 
   int too_long = 0;
   CUDA_TRY(h, cudaMemcpyAsync(&too_long, flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CUDA_TRY(h, cudaStreamSynchronize(h->stream));
-  if (too_long) return fail(h, B200SP_ERR_INVALID, "csr_sort_indices: an unsorted row has more than %d entries", cap);
-  return B200SP_OK;
+  if (!too_long) return B200SP_OK;
+  // a row longer than the shared-memory sort, or duplicate columns (whose order must be kept): stable radix sort
+  return dtype == B200SP_R_32F ? run_sort_indices_stable<float>(h, m, nnz, dAp, dAj, (float *)dAx)
+                               : run_sort_indices_stable<double>(h, m, nnz, dAp, dAj, (double *)dAx);
 }
 
 // ===================================== canonicalisation, dense, compare ====

@@ -167,6 +167,33 @@ int run_transpose(b200sp_context *h, int64_t nmajor, int64_t nminor, int64_t nnz
   return B200SP_OK;
 }
 
+// In-place stable in-row sort for any row length (the fallback of b200sp_csr_sort_indices): keys
+// (row << 32 | column), LSD passes over the column digits then the row digits (the input is grouped
+// by row already; the row passes restore the grouping), entries written to scratch and copied back.
+// Equal columns keep their storage order, as with cusparseXcsrsort + gather (cupyx/cusparse.py:832-866).
+template <typename T>
+int run_sort_indices_stable(b200sp_context *h, int64_t m, int64_t nnz, const int *Ap, int *Aj, T *Ax) {
+  SortScratch s;
+  TRY(carve_sort_scratch(h, nnz, s));
+  cudaStream_t st = h->stream;
+  CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, sizeof(int), st));
+  k_keys_from_compressed<true><<<flat_grid(h, m, 8), 256, 0, st>>>((int)m, INT_MAX, nnz, Ap, Aj, s.keys[0], s.flag);
+  TRY(check_launch(h, "k_keys_from_compressed"));
+  int cur = 0;
+  TRY(radix_sort(h, s, nnz, 31, bits_for(m), &cur));  // the column count is not an argument: all 31 index bits
+  int *idx_out = s.perm[cur ^ 1];
+  T *val_out = reinterpret_cast<T *>(s.keys[cur ^ 1]);
+  k_emit_sorted<T><<<flat_grid(h, nnz, 1024), 256, 0, st>>>(nnz, s.keys[cur], s.perm[cur], Ax, idx_out, val_out);
+  TRY(check_launch(h, "k_emit_sorted"));
+  int bad = 0;
+  CUDA_TRY(h, cudaMemcpyAsync(&bad, s.flag, sizeof(bad), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(h, cudaStreamSynchronize(st));
+  if (bad) return fail(h, B200SP_ERR_INVALID, "csr_sort_indices: negative index or malformed pointer array");
+  CUDA_TRY(h, cudaMemcpyAsync(Aj, idx_out, (size_t)nnz * sizeof(int), cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(h, cudaMemcpyAsync(Ax, val_out, (size_t)nnz * sizeof(T), cudaMemcpyDeviceToDevice, st));
+  return B200SP_OK;
+}
+
 }  // namespace
 
 extern "C" int b200sp_coo_to_csr(b200sp_handle_t h, int dtype, int64_t m, int64_t n, int64_t nnz,

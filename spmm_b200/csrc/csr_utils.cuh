@@ -29,8 +29,11 @@ k_csr_check_canonical(int m, int ncols, const int *__restrict__ Ap, const int *_
   if (__any_sync(FULL, bad) && lane == 0) atomicExch(flag, 1);
 }
 
-// CTA per row: rows of up to `cap` entries are sorted in shared memory (bitonic); longer rows
-// set *too_long (the host reports an error).  Rows already sorted are left untouched.
+// CTA per row: rows of up to `cap` entries are sorted in shared memory (bitonic).  Rows already
+// sorted are left untouched.  Longer rows, and rows that turn out to hold duplicate columns (the
+// bitonic network is not stable: duplicates would come out in another order than csrsort's stable
+// sort gives, and a later sum in storage order would round differently), are left as they are and
+// set *too_long: the host then runs the stable radix sort over the matrix.
 template <typename T>
 __global__ void __launch_bounds__(256)
 k_csr_sort_rows(int m, int cap, const int *__restrict__ Ap, int *__restrict__ Aj, T *__restrict__ Ax,
@@ -56,6 +59,12 @@ k_csr_sort_rows(int m, int cap, const int *__restrict__ Ap, int *__restrict__ Aj
     }
     __syncthreads();
     bitonic_sort(keys, vals, P, tid, 256, [] { __syncthreads(); });
+    int dup = 0;
+    for (int t = tid + 1; t < len; t += 256) dup |= (keys[t - 1] == keys[t]);
+    if (__syncthreads_or(dup)) {  // CTA-uniform
+      if (tid == 0) atomicExch(too_long, 1);
+      continue;
+    }
     for (int t = tid; t < len; t += 256) {
       Aj[b + t] = keys[t];
       Ax[b + t] = vals[t];

@@ -426,39 +426,51 @@ template <typename T> struct __align__(16) DenseSeg {
   T a;
 };
 
-// The pieces staged in s_seg[0 .. cnt) applied to the accumulator in order, one barrier per
-// piece.  Software pipeline: the (column, value) loads of pieces q+1 .. q+D are in flight while
-// piece q is applied (the L2 round trip is ~5 barrier steps long), and the staging entry of the
-// next fetch is read one step early, so nothing but the accumulator read itself waits on shared
-// memory.  The thread's index into a piece is clamped to the last entry of B, not to the piece:
-// lanes past its end load a neighbour's entry and discard it.
+// Staging of k_num_dense_cta, split in two arrays so that nothing but the loaded (column, value)
+// pairs rides in registers across the unrolled steps: the start of a piece is needed when its loads
+// are issued (D steps ahead), its length and A value when it is applied.  (One 16-byte entry read
+// with LDS.128 kept length and A value of all D pieces in flight in registers: 16 register moves per
+// 8 steps at the loop end - a tenth of the loop's instructions - and 2 wavefronts per read as well.)
+template <typename T> struct __align__(8) LenA {
+  int len;
+  T a;
+};
+
+// The pieces staged in s_start / s_la [0 .. cnt) applied to the accumulator in order, one barrier
+// per piece.  Software pipeline: the (column, value) loads of pieces q+1 .. q+D are in flight while
+// piece q is applied (the L2 round trip is ~5 barrier steps long), and the staging entries of the
+// next fetch and the next apply are read one step early, so nothing but the accumulator read itself
+// waits on shared memory.  The thread's index into a piece is clamped to the last entry of B, not to
+// the piece: lanes past its end load a neighbour's entry and discard it.
 template <typename T, int D>
-__device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const DenseSeg<T> *s_seg, int cnt, int tid,
-                                                   const int *__restrict__ Bj, const T *__restrict__ Bx, int last) {
-  int j[D], len[D];
-  T b[D], a[D];
-  DenseSeg<T> nx = s_seg[0];
-#define DENSE_FETCH(S, Q)                       \
-  {                                             \
-    len[S] = nx.len;                            \
-    a[S] = nx.a;                                \
-    const int idx_ = min(nx.start + tid, last); \
-    nx = s_seg[(Q) + 1];                        \
-    j[S] = ld_inplace(Bj + idx_);               \
-    b[S] = ld_inplace(Bx + idx_);               \
+__device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const int *s_start, const LenA<T> *s_la, int cnt,
+                                                   int tid, const int *__restrict__ Bj, const T *__restrict__ Bx, int last) {
+  int j[D];
+  T b[D];
+  int nstart = s_start[0];
+#define DENSE_FETCH(S, Q)                      \
+  {                                            \
+    const int idx_ = min(nstart + tid, last);  \
+    nstart = s_start[(Q) + 1];                 \
+    j[S] = ld_inplace(Bj + idx_);              \
+    b[S] = ld_inplace(Bx + idx_);              \
   }
 #pragma unroll
   for (int s = 0; s < D; ++s) DENSE_FETCH(s, s)
+  LenA<T> cu = s_la[0];
   for (int q = 0; q < cnt; q += D) {
 #pragma unroll
     for (int s = 0; s < D; ++s) {
       // the accumulator read goes first; the next fetch is issued underneath its latency
-      const bool piece = len[s] != 0;  // CTA-uniform; only the padding after the last piece is empty
-      const bool act = tid < len[s];
+      const int len = cu.len;
+      const T a = cu.a;
+      cu = s_la[q + s + 1];
+      const bool piece = len != 0;  // CTA-uniform; only the padding after the last piece is empty
+      const bool act = tid < len;
       T *slot = acc + j[s];
       T cur = T(0);
       if (act) cur = *slot;
-      const T prod = add_rn(mul_rn(a[s], b[s]), T(0));  // -0.0 -> +0.0
+      const T prod = add_rn(mul_rn(a, b[s]), T(0));  // -0.0 -> +0.0
       DENSE_FETCH(s, q + D + s)
       if (act) *slot = add_rn(cur, prod);
       if (piece) __syncthreads();
@@ -502,23 +514,42 @@ __device__ __forceinline__ int dense_count(const T *acc, int c_lo, int c_hi, int
 }
 
 // Ordered emit of that range, 32 columns per step (fully coalesced stores: the better choice for
-// well-filled rows).
+// well-filled rows).  `steps` = the trip count, a CTA-uniform upper bound of (c_hi - c_lo) / 32 that
+// the compiler can see is uniform (kernel parameters and blockDim only): with a loop bound derived
+// from the warp index it cannot prove the warp converged at the vote and wraps every ballot in a
+// BRA.DIV / BSSY / BSYNC sequence; and the stores are predicated on values computed outside the
+// `if`, so no branch is left (24.5 -> 14 instructions per 32 columns; the sweep was a third of all
+// instructions of the kernel on C3).
+// The three stores of one emitted entry under ONE predicate, without a branch (ptxas turns the `if`
+// into BSSY / BRA / BSYNC and sinks the address arithmetic into it).
+__device__ __forceinline__ void emit_if(bool p, int *cj, int col, float *cx, float v, float *slot, float unt) {
+  asm volatile(
+      "{\n.reg .pred q;\nsetp.ne.s32 q, %0, 0;\n@q st.global.s32 [%1], %2;\n@q st.global.f32 [%3], %4;\n@q st.shared.f32 [%5], %6;\n}\n" ::"r"((int)p),
+      "l"(cj), "r"(col), "l"(cx), "f"(v), "r"((unsigned)__cvta_generic_to_shared(slot)), "f"(unt)
+      : "memory");
+}
+__device__ __forceinline__ void emit_if(bool p, int *cj, int col, double *cx, double v, double *slot, double unt) {
+  asm volatile(
+      "{\n.reg .pred q;\nsetp.ne.s32 q, %0, 0;\n@q st.global.s32 [%1], %2;\n@q st.global.f64 [%3], %4;\n@q st.shared.f64 [%5], %6;\n}\n" ::"r"((int)p),
+      "l"(cj), "r"(col), "l"(cx), "d"(v), "r"((unsigned)__cvta_generic_to_shared(slot)), "d"(unt)
+      : "memory");
+}
+
 template <typename T, bool SCALE>
-__device__ __forceinline__ void dense_emit_ballot(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ Cj,
+__device__ __forceinline__ void dense_emit_ballot(T *acc, int c_lo, int c_hi, int steps, int lane, int *__restrict__ Cj,
                                                   T *__restrict__ Cx, int pos, T alpha, int col0 = 0) {
   const T UNT = NegZero<T>::value();
   const unsigned below = (1u << lane) - 1u;
+  int c = c_lo + lane;
 #pragma unroll 4
-  for (int c = c_lo + lane; c < c_hi; c += 32) {
-    const T v = acc[c];
+  for (int it = 0; it < steps; ++it, c += 32) {
+    const bool in = c < c_hi;
+    const T v = in ? acc[c] : UNT;
     const bool touched = !NegZero<T>::is(v);
     const unsigned bal = __ballot_sync(FULL, touched);
-    if (touched) {
-      const int o = pos + __popc(bal & below);
-      Cj[o] = col0 + c;
-      Cx[o] = SCALE ? mul_rn(alpha, v) : v;
-      acc[c] = UNT;
-    }
+    const int o = pos + __popc(bal & below);
+    const T out = SCALE ? mul_rn(alpha, v) : v;
+    emit_if(touched, Cj + o, col0 + c, Cx + o, out, acc + c, UNT);
     pos += __popc(bal);
   }
 }
@@ -526,12 +557,13 @@ __device__ __forceinline__ void dense_emit_ballot(T *acc, int c_lo, int c_hi, in
 // Ordered emit of that range, 128 columns per step: lane l owns columns c+4l .. c+4l+3, a warp
 // scan of the per-lane counts gives its output offset; the accumulator is reset on the way.
 template <typename T, bool SCALE>
-__device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int lane, int *__restrict__ Cj,
+__device__ __forceinline__ void dense_emit(T *acc, int c_lo, int c_hi, int steps, int lane, int *__restrict__ Cj,
                                            T *__restrict__ Cx, int pos, T alpha, int col0 = 0) {
   const T UNT = NegZero<T>::value();
-  for (int c = c_lo + 4 * lane; c < c_hi; c += 128) {
-    T v[4];
-    Vec4<T>::load(acc + c, v);
+  int c = c_lo + 4 * lane;
+  for (int it = 0; it < steps; ++it, c += 128) {  // uniform trip count (see dense_emit_ballot): the shuffles stay on the converged path
+    T v[4] = {UNT, UNT, UNT, UNT};
+    if (c < c_hi) Vec4<T>::load(acc + c, v);
     bool t[4];
     int cnt = 0;
 #pragma unroll
@@ -618,7 +650,8 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
                 const int *__restrict__ Bj, const T *__restrict__ Bx, int nnzB, const int *__restrict__ Cp,
                 int *__restrict__ Cj, T *__restrict__ Cx, T alpha, SinglePassArgs sp) {
   extern __shared__ __align__(16) unsigned char smem_raw[];  // round_up(n, 128) accumulator columns
-  __shared__ DenseSeg<T> s_seg[DENSE_CAP + DENSE_PAD];       // the staged pieces of the round
+  __shared__ int s_start[DENSE_CAP + DENSE_PAD];             // the staged pieces of the round: first entry in B ...
+  __shared__ LenA<T> s_la[DENSE_CAP + DENSE_PAD];            // ... length and A value
   __shared__ int s_wcnt[DENSE_MAX_NT / 32];
   __shared__ int s_scan[DENSE_MAX_NT / 32];
   __shared__ int s_row;
@@ -680,21 +713,21 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
         const int cnt = min(DENSE_CAP, total - r0);
         const int p_lo = max(0, r0 - off), p_hi = min(pieces, r0 + DENSE_CAP - off);
         for (int pc = p_lo; pc < p_hi; ++pc) {
-          DenseSeg<T> sg;
-          sg.start = start + pc * NT;
-          sg.len = min(NT, len - pc * NT);
-          sg.a = av;
-          s_seg[off + pc - r0] = sg;
+          LenA<T> la;
+          la.len = min(NT, len - pc * NT);
+          la.a = av;
+          s_start[off + pc - r0] = start + pc * NT;
+          s_la[off + pc - r0] = la;
         }
         if (tid < DENSE_PAD) {
-          DenseSeg<T> z;
-          z.start = 0;
+          LenA<T> z;
           z.len = 0;
           z.a = T(0);
-          s_seg[cnt + tid] = z;
+          s_start[cnt + tid] = 0;
+          s_la[cnt + tid] = z;
         }
         __syncthreads();
-        dense_apply_staged<T, DENSE_DEPTH>(acc, s_seg, cnt, tid, Bj, Bx, nnzB - 1);
+        dense_apply_staged<T, DENSE_DEPTH>(acc, s_start, s_la, cnt, tid, Bj, Bx, nnzB - 1);
         __syncthreads();
       }
       if (total == 0) __syncthreads();  // s_scan is rewritten by the next chunk
@@ -729,11 +762,11 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
     // well-filled rows: 32 columns per step with fully coalesced stores; sparse rows: 128 columns
     // per step (a quarter of the instructions, stores strided by the fill)
     if (row_nnz > (npad >> 2)) {
-      if (alpha == T(1)) dense_emit_ballot<T, false>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
-      else dense_emit_ballot<T, true>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
+      if (alpha == T(1)) dense_emit_ballot<T, false>(acc, c_lo, c_hi, cpw >> 5, lane, Cj, Cx, pos, alpha);
+      else dense_emit_ballot<T, true>(acc, c_lo, c_hi, cpw >> 5, lane, Cj, Cx, pos, alpha);
     } else {
-      if (alpha == T(1)) dense_emit<T, false>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
-      else dense_emit<T, true>(acc, c_lo, c_hi, lane, Cj, Cx, pos, alpha);
+      if (alpha == T(1)) dense_emit<T, false>(acc, c_lo, c_hi, cpw >> 7, lane, Cj, Cx, pos, alpha);
+      else dense_emit<T, true>(acc, c_lo, c_hi, cpw >> 7, lane, Cj, Cx, pos, alpha);
     }
     __syncthreads();
   }

@@ -153,6 +153,38 @@ def test_csr_sum_duplicates_bitwise(dt):
 
 
 @pytest.mark.parametrize("dt", [np.float32, np.float64])
+def test_sort_indices_long_rows_and_duplicates_stable(dt):
+    """csr_matrix.sort_indices() (csrsort + gather, cupyx/cusparse.py:832-866): rows longer than the
+    shared-memory sort (an R-MAT hub row of a raw product) and rows with duplicate columns go through
+    the stable radix sort - equal columns keep their storage order, so a later sum in storage order
+    gives the bits of scipy's sum_duplicates on the same input."""
+    import spmm_b200
+    rng = np.random.default_rng(3)
+    n = 90000
+    lens = [60000, 0, 5, 17000, 300, 1, 40000, 16385, 2]
+    cols = [rng.permutation(n)[:L] for L in lens]               # unsorted, distinct
+    cols[4] = rng.integers(0, 40, lens[4])                      # short row, many duplicates
+    cols[6] = rng.integers(0, 5000, lens[6])                    # long row with duplicates
+    indices = np.concatenate(cols).astype(np.int32)
+    indptr = np.concatenate(([0], np.cumsum(lens))).astype(np.int32)
+    data = rng.standard_normal(indices.size).astype(dt)
+    M = spmm_b200.csr_matrix((data, indices, indptr), shape=(len(lens), n))
+    M.sort_indices()
+    gp, gj, gx = _csr_np(M)
+    assert np.array_equal(gp, indptr)
+    for r in range(len(lens)):
+        b, e = indptr[r], indptr[r + 1]
+        order = np.argsort(indices[b:e], kind="stable")
+        assert np.array_equal(gj[b:e], indices[b:e][order]), f"row {r}: columns"
+        assert np.array_equal(gx[b:e].view(np.uint8), data[b:e][order].view(np.uint8)), f"row {r}: values not in stable order"
+    # an already sorted, duplicate-free matrix is left alone (no fallback, same arrays)
+    S = helpers.profiler_matrix(300, 5000, 0.05, seed=8, dtype=dt)
+    T = spmm_b200.csr_matrix(S)
+    T.sort_indices()
+    helpers.assert_csr_bitwise(_csr_np(T), helpers.triple(S), "sorted input")
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
 def test_toarray_and_max_abs_diff(dt):
     import spmm_b200
     A = helpers.random_csr(300, 170, 0.1, 1, dtype=dt)

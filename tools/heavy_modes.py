@@ -37,8 +37,14 @@ CONFIGS = {
     "blocked_w8_f64": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "8", "B200SP_FLAT_BELOW": "64"},
     "blocked_w8_f96": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "8", "B200SP_FLAT_BELOW": "96"},
     "blocked_w8_f128": {"B200SP_HEAVY": "blocked", "B200SP_WINDOW_TURN": "8", "B200SP_FLAT_BELOW": "128"},
+    # CTA shape of the blocked kernel: threads per CTA (= longest piece per barrier step) and accumulator kilobytes per CTA
+    "nt128_kb100": {"B200SP_HEAVY": "blocked", "B200SP_BLOCKED_NT": "128", "B200SP_BLOCKED_KB": "100"},
+    "nt128_kb64": {"B200SP_HEAVY": "blocked", "B200SP_BLOCKED_NT": "128", "B200SP_BLOCKED_KB": "64"},
+    "nt128_kb48": {"B200SP_HEAVY": "blocked", "B200SP_BLOCKED_NT": "128", "B200SP_BLOCKED_KB": "48"},
+    "nt256_kb48": {"B200SP_HEAVY": "blocked", "B200SP_BLOCKED_NT": "256", "B200SP_BLOCKED_KB": "48"},
+    "nt256_kb200": {"B200SP_HEAVY": "blocked", "B200SP_BLOCKED_NT": "256", "B200SP_BLOCKED_KB": "200"},
 }
-KEYS = ("B200SP_HEAVY", "B200SP_RANK_ACC_KB", "B200SP_HEAVY_MIN", "B200SP_HEAVY_DENSE_DIV", "B200SP_WINDOW_TURN", "B200SP_FLAT_BELOW")
+KEYS = ("B200SP_BLOCKED_NT", "B200SP_BLOCKED_KB", "B200SP_HEAVY", "B200SP_RANK_ACC_KB", "B200SP_HEAVY_MIN", "B200SP_HEAVY_DENSE_DIV", "B200SP_WINDOW_TURN", "B200SP_FLAT_BELOW")
 
 
 def run_once(A, b, rp, dev):
