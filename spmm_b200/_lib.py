@@ -9,7 +9,8 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200sp.so")
+# B200SP_LIB: another build of the same ABI (A/B timing of two library versions inside one GPU call)
+LIB_PATH = os.environ.get("B200SP_LIB") or os.path.join(_HERE, "libb200sp.so")
 
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_ALLOC, ERR_OVERFLOW, ERR_STATE, ERR_IO = -1, -2, -3, -4, -5, -6

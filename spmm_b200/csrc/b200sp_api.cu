@@ -22,6 +22,7 @@
 #include "spgemm_setup.cuh"
 #include "spgemm_symbolic.cuh"
 #include "spgemm_rank.cuh"
+#include "spgemm_warp.cuh"
 #include "spmv.cuh"
 #include "csr_utils.cuh"
 #include "convert.cuh"
@@ -46,7 +47,7 @@ struct Buffer {  // grow-only device buffer
 };
 
 enum SymKind { SYM_GROUP8, SYM_WARP, SYM_CTA_HASH, SYM_CTA_BITMAP };
-enum NumKind { NUM_GROUP8, NUM_WARP, NUM_CTA_HASH, NUM_GLOBAL, NUM_DENSE, NUM_DENSE_BLOCKED, NUM_RANK };
+enum NumKind { NUM_GROUP8, NUM_WARP, NUM_CTA_HASH, NUM_GLOBAL, NUM_DENSE, NUM_DENSE_BLOCKED, NUM_RANK, NUM_WARP_BLOCKS };
 
 struct BinPlan {
   int kind;
@@ -403,7 +404,8 @@ void plan_bins(Plan &p) {
     // default: blocked.  Measured on B200 (profiles/r02_heavy_modes_v16.jsonl, whole A @ A incl. symbolic):
     // R-MAT scale 16 / 18 / 20: blocked 7.3 / 56 / 698 ms, rank (96 KB) 9.8 / 73 / 927 ms, mixed (n/8) 8.4 / 68 / 848 ms
     const bool want_rank = mode && strcmp(mode, "rank") == 0;
-    const bool want_blocked = blocked_ok && !want_rank && !(mode && strcmp(mode, "mixed") == 0);
+    const bool want_warp = mode && strcmp(mode, "warp") == 0;  // k_num_warp_blocks (falls back to blocked when its table would not fit)
+    const bool want_blocked = blocked_ok && !want_rank && !want_warp && !(mode && strcmp(mode, "mixed") == 0);
     const bool want_mixed = blocked_ok && mode && strcmp(mode, "mixed") == 0;
     int t_dense = std::max(512, std::min(6144, p.n / 128));
     if (tmin && atoi(tmin) >= 512) t_dense = std::min(6144, atoi(tmin));
@@ -412,7 +414,10 @@ void plan_bins(Plan &p) {
       p.num_limits.limit[nb] = t_dense;
       p.num_bins[nb++] = {NUM_CTA_HASH, 8192};
     }
-    if (want_blocked) {
+    if (want_warp) {
+      p.num_limits.limit[nb] = INT_MAX;
+      p.num_bins[nb++] = {NUM_WARP_BLOCKS, 0};
+    } else if (want_blocked) {
       p.num_limits.limit[nb] = INT_MAX;
       p.num_bins[nb++] = {NUM_DENSE_BLOCKED, 0};
     } else if (want_mixed) {
@@ -486,6 +491,23 @@ int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
   return fail(h, B200SP_ERR_INVALID, "bad symbolic bin kind");
 }
 
+// The packed, bank-dealt copy of B the dense kernel reads (spgemm_numeric.cuh: k_pack_b), rebuilt by every
+// value pass (the values may be new) into ws3: one kernel over B, ~10 us on C3.
+template <typename T>
+int pack_b(b200sp_context *h, const T *Bx, const PBEnt<T> **pb, int *pb_last) {
+  Plan &p = h->plan;
+  const size_t entries = (((size_t)p.nnzB + 31) & ~(size_t)31) + 32 * (size_t)p.k;
+  if (entries > (size_t)INT32_MAX) return fail(h, B200SP_ERR_OVERFLOW, "packed copy of B does not fit int32 offsets");
+  TRY(ensure(h, h->ws3, entries * sizeof(PBEnt<T>)));
+  p.bounds_nblk = p.bounds_W = 0;  // ws3 no longer holds a block-boundary table
+  const int grid = std::max(1, std::min((p.k + 7) / 8, h->num_sms * 8));
+  k_pack_b<T><<<grid, 256, 0, h->stream>>>(p.k, p.Bp, p.Bj, Bx, (PBEnt<T> *)h->ws3.ptr);
+  TRY(check_launch(h, "k_pack_b"));
+  *pb = (const PBEnt<T> *)h->ws3.ptr;
+  *pb_last = (int)entries - 1;
+  return B200SP_OK;
+}
+
 template <typename T>
 int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alpha, const T *Ax,
                        const T *Bx, int *Cj, T *Cx) {
@@ -521,8 +543,11 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         const size_t smem = (((size_t)p.n + 127) & ~(size_t)127) * sizeof(T);  // padded to whole 128-column groups
         const double avgB = p.k ? (double)p.nnzB / (double)p.k : 0.0;
         const int nt = std::max(64, std::min(DENSE_MAX_NT, (int)((avgB + 31) / 32) * 32));
+        const PBEnt<T> *pb = nullptr;
+        int pb_last = 0;
+        TRY(pack_b<T>(h, Bx, &pb, &pb_last));
         TRY(set_smem(h, k_num_dense_cta<T, false>, smem));
-        k_num_dense_cta<T, false><<<persistent_grid(h, cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, SinglePassArgs{});
+        k_num_dense_cta<T, false><<<persistent_grid(h, cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, pb, pb_last, p.Cp, Cj, Cx, alpha, SinglePassArgs{});
         return check_launch(h, "k_num_dense_cta");
       }
       // fp64 with n between the fp32 and fp64 budgets: column blocks
@@ -569,6 +594,45 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       }
       // B not canonical (or absurdly wide): the global-memory kernel takes any input
       goto global_fallback;
+    case NUM_WARP_BLOCKS: {
+      int WW = sizeof(T) == 4 ? 2560 : 1280;  // 10 KB of accumulator per warp: 16 warps per SM
+      if (const char *e = getenv("B200SP_WARP_WW")) {
+        const int v = atoi(e) & ~31;
+        if (v >= 256 && v <= 16384) WW = v;
+      }
+      const int nblk = (p.n + WW - 1) / WW;
+      const size_t table = (size_t)p.k * (nblk + 1) * sizeof(int);
+      if (!p.b_canonical || table > ((size_t)3 << 30) || (long long)cnt * nblk > (long long)INT32_MAX - 2 * WB_CHUNK) {
+        // the boundary table or the task ids would not fit: the CTA-per-block kernel takes these rows
+        BinPlan saved = p.num_bins[b];
+        p.num_bins[b].kind = NUM_DENSE_BLOCKED;
+        const int rc = launch_numeric_bin<T>(h, b, rows, cnt, alpha, Ax, Bx, Cj, Cx);
+        p.num_bins[b] = saved;
+        return rc;
+      }
+      if (p.bounds_nblk != nblk || p.bounds_W != WW) {
+        const size_t total = (size_t)p.k * (nblk + 1);
+        TRY(ensure(h, h->ws3, 256 + total * sizeof(int)));  // [row ticket | pad | table]
+        const int bgrid = (int)std::max<size_t>(1, std::min<size_t>((total + 255) / 256, (size_t)h->num_sms * 16));
+        k_block_bounds<<<bgrid, 256, 0, st>>>(p.k, nblk, WW, p.Bp, p.Bj, (int *)h->ws3.ptr + 64);
+        TRY(check_launch(h, "k_block_bounds"));
+        p.bounds_nblk = nblk;
+        p.bounds_W = WW;
+      }
+      const size_t per_warp = ((size_t)WW * sizeof(T) + (size_t)(WB_Q + WB_QPAD) * (sizeof(WbStep) + sizeof(T)) + (size_t)(WW / 32) * 4 + 15) & ~(size_t)15;
+      const size_t smem = per_warp * (WB_NT / 32);
+      TRY(set_smem(h, k_num_warp_blocks<T>, smem));
+      int per_sm = 1;
+      CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_warp_blocks<T>, WB_NT, smem));
+      const long long ntasks = (long long)cnt * nblk;
+      const long long want = (ntasks + WB_CHUNK * (WB_NT / 32) - 1) / (WB_CHUNK * (WB_NT / 32));
+      const int grid = (int)std::max<long long>(1, std::min<long long>(want, (long long)h->num_sms * std::max(1, per_sm)));
+      TRY(ensure(h, h->ws2, (size_t)ntasks * sizeof(unsigned)));  // per-task status words of the look-back
+      CUDA_TRY(h, cudaMemsetAsync(h->ws2.ptr, 0, (size_t)ntasks * sizeof(unsigned), st));
+      CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, sizeof(int), st));  // the task ticket
+      k_num_warp_blocks<T><<<grid, WB_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, WW, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, (unsigned *)h->ws2.ptr);
+      return check_launch(h, "k_num_warp_blocks");
+    }
     case NUM_RANK: {
       size_t acc_bytes = SMEM_RANK_ACC;
       if (const char *kb = getenv("B200SP_RANK_ACC_KB")) {
@@ -875,8 +939,11 @@ int run_single_pass(b200sp_context *h, const void *alpha, const void *Ax, const 
   CUDA_TRY(h, cudaMemsetAsync(status, 0, (size_t)p.m * 8, st));
   CUDA_TRY(h, cudaMemsetAsync(&ctr->num_cursor[0], 0, sizeof(int), st));  // the row ticket
   SinglePassArgs sp{&ctr->num_cursor[0], status, p.Cp, &ctr->nnz_c};
-  k_num_dense_cta<T, true><<<grid, nt, smem, st>>>(nullptr, p.m, p.n, p.Ap, p.Aj, (const T *)Ax, p.Bp, p.Bj, (const T *)Bx,
-                                                  (int)p.nnzB, nullptr, Cj, (T *)Cx, a, sp);
+  const PBEnt<T> *pb = nullptr;
+  int pb_last = 0;
+  TRY(pack_b<T>(h, (const T *)Bx, &pb, &pb_last));
+  k_num_dense_cta<T, true><<<grid, nt, smem, st>>>(nullptr, p.m, p.n, p.Ap, p.Aj, (const T *)Ax, p.Bp, pb, pb_last, nullptr, Cj,
+                                                  (T *)Cx, a, sp);
   return check_launch(h, "k_num_dense_cta<single pass>");
 }
 

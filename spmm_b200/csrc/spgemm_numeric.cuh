@@ -426,6 +426,105 @@ template <typename T> struct __align__(16) DenseSeg {
   T a;
 };
 
+// ---- packed, bank-dealt copy of B for k_num_dense_cta --------------------------------------------
+// The L1 data pipe is what bounds the kernel (73 % busy on C3: 243 M wavefronts per launch, of them
+// 78 M bank-conflict replays of the accumulator read-modify-write and ~65 M for the two 4-byte loads
+// of a (column, value) pair, each straddling two 128-byte lines).  Both come from how a B row lies
+// in memory, and the order of the entries INSIDE a B row changes no bit of C (its columns are
+// distinct), so every numeric call first writes B once more (one kernel, ~2 x 8 nnzB bytes):
+//   * (column, value) interleaved: one 8-byte (fp64: 16-byte) load per product instead of two;
+//   * every row starts on a 32-entry boundary and is padded to whole groups of 32 entries (column -1
+//     = no entry), so a warp's load is one aligned 256-byte span;
+//   * inside a row the entries are dealt over its groups of 32 like cards, sorted by accumulator
+//     bank (column mod 32; fp64: mod 16): a group - what one warp applies in one step - holds every
+//     bank about once.
+// Row kk occupies [ru32(Bp[kk]) + 32 kk, + ru32(len)) in entries: closed form, no scan, no second
+// pointer array; the 32 spare entries per row are never read.
+template <typename T> struct PBEnt;
+template <> struct __align__(8) PBEnt<float> {
+  int col;
+  float val;
+};
+template <> struct __align__(16) PBEnt<double> {
+  int col, pad;
+  double val;
+};
+__device__ __forceinline__ int pb_start(int bp, int kk) { return ((bp + 31) & ~31) + 32 * kk; }
+__device__ __forceinline__ void ld_pb(const PBEnt<float> *p, int &col, float &val) {
+  asm volatile("ld.global.v2.b32 {%0, %1}, [%2];" : "=r"(col), "=f"(val) : "l"(p));
+}
+__device__ __forceinline__ void ld_pb(const PBEnt<double> *p, int &col, double &val) {
+  long long c;
+  asm volatile("ld.global.v2.b64 {%0, %1}, [%2];" : "=l"(c), "=d"(val) : "l"(p));
+  col = (int)c;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_pack_b(int k, const int *__restrict__ Bp, const int *__restrict__ Bj, const T *__restrict__ Bx,
+         PBEnt<T> *__restrict__ pb) {
+  constexpr int BANKS = sizeof(T) == 4 ? 32 : 16;
+  __shared__ int s_base[8][32];
+  const int lane = lane_id(), w = threadIdx.x >> 5;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const unsigned lt = (1u << lane) - 1u;
+  for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < k; r += warps) {
+    const int b = __ldg(Bp + r), L = __ldg(Bp + r + 1) - b;
+    if (L <= 0) continue;
+    PBEnt<T> *row = pb + pb_start(b, r);
+    const int G = (L + 31) >> 5;  // groups of 32 entries
+    const float rG = 1.0f / (float)G;
+    s_base[w][lane] = 0;
+    __syncwarp();
+    for (int t = lane; t < L; t += 32) atomicAdd(&s_base[w][__ldg(Bj + b + t) & (BANKS - 1)], 1);
+    __syncwarp();
+    const int c = s_base[w][lane];
+    int inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(FULL, inc, o);
+      if (lane >= o) inc += u;
+    }
+    __syncwarp();
+    s_base[w][lane] = inc - c;  // first rank of the bank in the row's bank-sorted order
+    __syncwarp();
+    for (int t0 = 0; t0 < L; t0 += 32) {
+      const int t = t0 + lane;
+      const bool valid = t < L;
+      const int col = valid ? __ldg(Bj + b + t) : 0;
+      const T val = valid ? __ldg(Bx + b + t) : T(0);
+      const int bank = col & (BANKS - 1);
+      const unsigned peers = __match_any_sync(FULL, valid ? bank : 32 + lane);
+      const int r_in = __popc(peers & lt);
+      int sidx = 0;
+      if (valid) sidx = s_base[w][bank] + r_in;
+      __syncwarp();
+      if (valid && r_in == __popc(peers) - 1) s_base[w][bank] = sidx + 1;
+      __syncwarp();
+      if (valid) {
+        PBEnt<T> e;
+        e.col = col;
+        e.val = val;
+        int q = __float2int_rz((float)sidx * rG);  // sidx / G without the integer division (sidx < 2^24)
+        int g = sidx - q * G;
+        if (g >= G) g -= G, ++q;
+        if (g < 0) g += G, --q;
+        row[g * 32 + q] = e;  // dealt: consecutive ranks go to consecutive groups
+      }
+    }
+    // the slots no entry was dealt to: group g holds ceil((L - g) / G) entries = L / G, one more for g < L % G
+    const int qL = L / G, rL = L - qL * G;
+    for (int g = 0; g < G; ++g) {
+      if (lane >= qL + (g < rL)) {
+        PBEnt<T> e;
+        e.col = -1;
+        e.val = T(0);
+        row[(g << 5) + lane] = e;
+      }
+    }
+  }
+}
+
 // Staging of k_num_dense_cta, split in two arrays so that nothing but the loaded (column, value)
 // pairs rides in registers across the unrolled steps: the start of a piece is needed when its loads
 // are issued (D steps ahead), its length and A value when it is applied.  (One 16-byte entry read
@@ -444,7 +543,7 @@ template <typename T> struct __align__(8) LenA {
 // the piece: lanes past its end load a neighbour's entry and discard it.
 template <typename T, int D>
 __device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const int *s_start, const LenA<T> *s_la, int cnt,
-                                                   int tid, const int *__restrict__ Bj, const T *__restrict__ Bx, int last) {
+                                                   int tid, const PBEnt<T> *__restrict__ pb, int last) {
   int j[D];
   T b[D];
   int nstart = s_start[0];
@@ -452,8 +551,7 @@ __device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const in
   {                                            \
     const int idx_ = min(nstart + tid, last);  \
     nstart = s_start[(Q) + 1];                 \
-    j[S] = ld_inplace(Bj + idx_);              \
-    b[S] = ld_inplace(Bx + idx_);              \
+    ld_pb(pb + idx_, j[S], b[S]);              \
   }
 #pragma unroll
   for (int s = 0; s < D; ++s) DENSE_FETCH(s, s)
@@ -466,7 +564,7 @@ __device__ __forceinline__ void dense_apply_staged(T *__restrict__ acc, const in
       const T a = cu.a;
       cu = s_la[q + s + 1];
       const bool piece = len != 0;  // CTA-uniform; only the padding after the last piece is empty
-      const bool act = tid < len;
+      const bool act = tid < len && j[s] >= 0;  // inside the piece and not one of the row's padding slots
       T *slot = acc + j[s];
       T cur = T(0);
       if (act) cur = *slot;
@@ -647,7 +745,7 @@ template <typename T, bool SINGLE>
 __global__ void __launch_bounds__(DENSE_MAX_NT, 3)
 k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
                 const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
-                const int *__restrict__ Bj, const T *__restrict__ Bx, int nnzB, const int *__restrict__ Cp,
+                const PBEnt<T> *__restrict__ pb, int pb_last, const int *__restrict__ Cp,
                 int *__restrict__ Cj, T *__restrict__ Cx, T alpha, SinglePassArgs sp) {
   extern __shared__ __align__(16) unsigned char smem_raw[];  // round_up(n, 128) accumulator columns
   __shared__ int s_start[DENSE_CAP + DENSE_PAD];             // the staged pieces of the round: first entry in B ...
@@ -690,8 +788,9 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
       T av = T(0);
       if (t < a_end) {
         const int kk = __ldg(Aj + t);
-        start = __ldg(Bp + kk);
-        len = __ldg(Bp + kk + 1) - start;
+        const int bp = __ldg(Bp + kk);
+        start = pb_start(bp, kk);
+        len = (__ldg(Bp + kk + 1) - bp + 31) & ~31;  // the row in the packed copy: whole groups of 32 entries
         av = __ldg(Ax + t);
       }
       const int pieces = (len + NT - 1) / NT;  // 0 for an empty B row: it gets no slot at all
@@ -727,7 +826,7 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
           s_la[cnt + tid] = z;
         }
         __syncthreads();
-        dense_apply_staged<T, DENSE_DEPTH>(acc, s_start, s_la, cnt, tid, Bj, Bx, nnzB - 1);
+        dense_apply_staged<T, DENSE_DEPTH>(acc, s_start, s_la, cnt, tid, pb, pb_last);
         __syncthreads();
       }
       if (total == 0) __syncthreads();  // s_scan is rewritten by the next chunk

@@ -170,7 +170,8 @@ def test_heavy_rows_hubs_and_hot_columns(b200, dtype, alg, cf):
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("mode,acc_kb,tmin", [("rank", None, None), ("rank", "8", None), ("rank", "16", "512"),
-                                             ("blocked", None, None), ("mixed", "8", None)])
+                                             ("blocked", None, None), ("mixed", "8", None), ("warp", None, None),
+                                             ("warp", None, "512")])
 def test_heavy_row_kernels_all_modes(b200, dtype, mode, acc_kb, tmin, monkeypatch):
     """The heavy rows of wide matrices through every kernel choice: the compact rank accumulator
     (k_num_rank_cta; default), forced into many passes per row by a small accumulator (8 KB = 2048

@@ -43,8 +43,13 @@ CONFIGS = {
     "nt128_kb48": {"B200SP_HEAVY": "blocked", "B200SP_BLOCKED_NT": "128", "B200SP_BLOCKED_KB": "48"},
     "nt256_kb48": {"B200SP_HEAVY": "blocked", "B200SP_BLOCKED_NT": "256", "B200SP_BLOCKED_KB": "48"},
     "nt256_kb200": {"B200SP_HEAVY": "blocked", "B200SP_BLOCKED_NT": "256", "B200SP_BLOCKED_KB": "200"},
+    # one warp per (row, narrow block): k_num_warp_blocks, accumulator columns per warp
+    "warp": {"B200SP_HEAVY": "warp"},
+    "warp_ww1280": {"B200SP_HEAVY": "warp", "B200SP_WARP_WW": "1280"},
+    "warp_ww5120": {"B200SP_HEAVY": "warp", "B200SP_WARP_WW": "5120"},
+    "warp_t512": {"B200SP_HEAVY": "warp", "B200SP_HEAVY_MIN": "512"},
 }
-KEYS = ("B200SP_BLOCKED_NT", "B200SP_BLOCKED_KB", "B200SP_HEAVY", "B200SP_RANK_ACC_KB", "B200SP_HEAVY_MIN", "B200SP_HEAVY_DENSE_DIV", "B200SP_WINDOW_TURN", "B200SP_FLAT_BELOW")
+KEYS = ("B200SP_WARP_WW", "B200SP_BLOCKED_NT", "B200SP_BLOCKED_KB", "B200SP_HEAVY", "B200SP_RANK_ACC_KB", "B200SP_HEAVY_MIN", "B200SP_HEAVY_DENSE_DIV", "B200SP_WINDOW_TURN", "B200SP_FLAT_BELOW")
 
 
 def run_once(A, b, rp, dev):
