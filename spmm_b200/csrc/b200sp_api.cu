@@ -602,7 +602,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       }
       const int nblk = (p.n + WW - 1) / WW;
       const size_t table = (size_t)p.k * (nblk + 1) * sizeof(int);
-      if (!p.b_canonical || table > ((size_t)3 << 30) || (long long)cnt * nblk > (long long)INT32_MAX - 2 * WB_CHUNK) {
+      if (!p.b_canonical || table > ((size_t)3 << 30) || ((long long)cnt + WB_CHUNK) * nblk > (long long)INT32_MAX - 2 * WB_CHUNK) {
         // the boundary table or the task ids would not fit: the CTA-per-block kernel takes these rows
         BinPlan saved = p.num_bins[b];
         p.num_bins[b].kind = NUM_DENSE_BLOCKED;
@@ -624,13 +624,13 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       TRY(set_smem(h, k_num_warp_blocks<T>, smem));
       int per_sm = 1;
       CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_warp_blocks<T>, WB_NT, smem));
-      const long long ntasks = (long long)cnt * nblk;
+      const long long ntasks = (long long)cnt * nblk;  // status words; the ticket runs over whole sets of WB_CHUNK rows
       const long long want = (ntasks + WB_CHUNK * (WB_NT / 32) - 1) / (WB_CHUNK * (WB_NT / 32));
       const int grid = (int)std::max<long long>(1, std::min<long long>(want, (long long)h->num_sms * std::max(1, per_sm)));
       TRY(ensure(h, h->ws2, (size_t)ntasks * sizeof(unsigned)));  // per-task status words of the look-back
       CUDA_TRY(h, cudaMemsetAsync(h->ws2.ptr, 0, (size_t)ntasks * sizeof(unsigned), st));
       CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, sizeof(int), st));  // the task ticket
-      k_num_warp_blocks<T><<<grid, WB_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, WW, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, (unsigned *)h->ws2.ptr);
+      k_num_warp_blocks<T><<<grid, WB_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, WW, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, getenv("B200SP_WB_NOWAIT") ? nullptr : (unsigned *)h->ws2.ptr);
       return check_launch(h, "k_num_warp_blocks");
     }
     case NUM_RANK: {

@@ -9,8 +9,8 @@
 //
 // Here the unit of work is a warp with its own accumulator of WW columns (10 KB) and its own
 // touched-column bitmap: 16 independent warps per SM, no CTA barrier anywhere.  A task is a
-// (row, block) pair; tasks are handed out in (row, block) order by a global ticket, a few at a
-// time.  Per task the warp
+// (row, block) pair; tasks are handed out by a global ticket, a few at a time (the same block of a
+// few consecutive rows).  Per task the warp
 //   1. visits the row's A entries 128 at a time, lane-parallel: the segment of B row k inside the
 //      block is [bounds[k][b], bounds[k][b+1]) (the table of k_block_bounds at WW granularity),
 //      empty segments cost nothing further;
@@ -132,7 +132,12 @@ k_num_warp_blocks(const int *__restrict__ rows, int nrows, int *__restrict__ tic
   for (int c = lane; c < WW; c += 32) acc[c] = UNT;
   for (int c = lane; c < nw; c += 32) bm[c] = 0u;
   __syncwarp();
-  const long long ntasks = (long long)nrows * nblk;
+  // Task order: rows in sets of WB_CHUNK; inside a set block after block, and inside a block the set's rows.
+  // The WB_CHUNK consecutive tasks one ticket hands to a warp are therefore the SAME block of DIFFERENT rows:
+  // a task waits for the counts of its row's earlier blocks, and with consecutive blocks of one row in one
+  // warp (first version) every row was processed serially along that chain (R-MAT scale 18: 1140 ms).
+  const int nsets = (nrows + WB_CHUNK - 1) / WB_CHUNK;
+  const long long ntasks = (long long)nsets * WB_CHUNK * nblk;
   const int stride = nblk + 1;
   for (;;) {
     int t0 = 0;
@@ -141,7 +146,9 @@ k_num_warp_blocks(const int *__restrict__ rows, int nrows, int *__restrict__ tic
     if (t0 >= ntasks) break;
     const int t1 = (int)min((long long)t0 + WB_CHUNK, ntasks);
     for (int t = t0; t < t1; ++t) {
-      const int ridx = t / nblk, b = t - ridx * nblk;
+      const int set = t / (WB_CHUNK * nblk), rem = t - set * (WB_CHUNK * nblk);
+      const int b = rem / WB_CHUNK, ridx = set * WB_CHUNK + (rem - b * WB_CHUNK);
+      if (ridx >= nrows) continue;  // the last set may be short
       const int row = __ldg(rows + ridx);
       const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
       const int c0 = b * WW;
@@ -202,7 +209,7 @@ k_num_warp_blocks(const int *__restrict__ rows, int nrows, int *__restrict__ tic
       int mine_cnt = 0;
       for (int i = lane; i < nw; i += 32) mine_cnt += __popc(bm[i]);
       const int own = warp_sum(mine_cnt);
-      const int excl = wb_lookback(status, t, b, own, lane);
+      const int excl = status ? wb_lookback(status, (long long)ridx * nblk + b, b, own, lane) : 0;  // status == nullptr: timing experiment only (wrong offsets)
       if (own == 0) continue;  // warp-uniform
       int out = __ldg(Cp + row) + excl;
       for (int i0 = 0; i0 < nw; i0 += 32) {
