@@ -142,6 +142,22 @@ int b200sp_spgemm_single_pass(b200sp_handle_t handle, int dtype, const void *alp
                               int64_t *nnzC);
 
 /*
+ * The single pass without the estimate's host synchronisation, for callers that can tell from the
+ * sizes alone that C will be well filled (the Python operator does when nnzA * nnzB / k >= m * n / 2):
+ * the caller allocates dCj / dCx at the bound that needs no estimate, capacity >= m * n entries, and
+ * the products-per-row kernel, the canonical check of B, the packing of B and the single-pass kernel
+ * are enqueued back to back; the kernel itself does nothing if the check of B failed.  ONE host sync
+ * at the end returns *nnzC and *num_products (B200SP_ERR_INVALID for non-canonical B).  Same bits as
+ * every other mode.  Requires n * sizeof(value) <= 208 KB and m * n <= 2^31 - 1.  Replaces the same
+ * reference calls as b200sp_spgemm_estimate + b200sp_spgemm_single_pass.
+ */
+int b200sp_spgemm_single_pass_direct(b200sp_handle_t handle, int dtype, int64_t m, int64_t k, int64_t n,
+                                     int64_t nnzA, int64_t nnzB, const int32_t *dAp, const int32_t *dAj,
+                                     const void *dAx, const int32_t *dBp, const int32_t *dBj,
+                                     const void *dBx, const void *alpha, int32_t *dCp, int32_t *dCj,
+                                     void *dCx, int64_t capacity, int64_t *nnzC, int64_t *num_products);
+
+/*
  * Numeric phase: fills dCj (nnzC int32) and dCx (nnzC values), both caller owned, allocated
  * after reading nnzC exactly like cusparse.py:2128-2131 / alg1.cu:184-186.
  * Replaces the value half of cusparseSpGEMM_compute and cusparseSpGEMM_copy (alg1.cu:187-188,

@@ -52,6 +52,9 @@ SYMBOLS = [
      [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, ctypes.c_int, ctypes.c_float,
       c_vp, i64p, i64p, ctypes.POINTER(ctypes.c_int)]),
     ("b200sp_spgemm_single_pass", ctypes.c_int, [c_vp, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, i64p]),
+    ("b200sp_spgemm_single_pass_direct", ctypes.c_int,
+     [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+      c_i64, i64p, i64p]),
     ("b200sp_spgemm_numeric", ctypes.c_int, [c_vp, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp]),
     ("b200sp_spgemm_host", ctypes.c_int,
      [c_vp, ctypes.c_int, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_int,

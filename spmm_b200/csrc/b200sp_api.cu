@@ -709,7 +709,7 @@ WsLayout ws_layout(int m) {
 // of nnz(C), the symbolic bins, the canonical check of B.  Ends with host sync #1.
 int spgemm_stage1(b200sp_context *h, int64_t m, int64_t k, int64_t n, int64_t nnzA, int64_t nnzB,
                   const int32_t *dAp, const int32_t *dAj, const int32_t *dBp, const int32_t *dBj, int alg,
-                  float chunk_fraction, int32_t *dCp) {
+                  float chunk_fraction, int32_t *dCp, bool enqueue_only = false) {
   Plan &p = h->plan;
   p.valid = false;
   p.stage1 = false;
@@ -770,6 +770,10 @@ int spgemm_stage1(b200sp_context *h, int64_t m, int64_t k, int64_t n, int64_t nn
     const int cgrid = std::max(1, std::min((int)((k + 7) / 8), h->num_sms * 8));
     k_csr_check_canonical<<<cgrid, 256, 0, st>>>(p.k, p.n, dBp, dBj, &ctr->b_bad);
     TRY(check_launch(h, "k_csr_check_canonical"));
+  }
+  if (enqueue_only) {  // b200sp_spgemm_single_pass_direct: no row lists, and the counters are read once, at its end
+    cudaEventRecord(h->ev[1], st);
+    return B200SP_OK;
   }
   const int sgrid = std::max(1, std::min((p.m + 255) / 256, h->num_sms * 8));
   k_scatter_rows<false><<<sgrid, 256, 0, st>>>(p.m, rowub, p.sym_limits, ctr, p.rows_sym);
@@ -914,7 +918,8 @@ extern "C" int b200sp_spgemm_symbolic(b200sp_handle_t h, int64_t m, int64_t k, i
 namespace {
 
 template <typename T>
-int run_single_pass(b200sp_context *h, const void *alpha, const void *Ax, const void *Bx, int *Cj, void *Cx) {
+int run_single_pass(b200sp_context *h, const void *alpha, const void *Ax, const void *Bx, int *Cj, void *Cx,
+                    bool guarded = false) {
   Plan &p = h->plan;
   const T a = alpha ? *(const T *)alpha : T(1);
   cudaStream_t st = h->stream;
@@ -938,7 +943,7 @@ int run_single_pass(b200sp_context *h, const void *alpha, const void *Ax, const 
   const int grid = std::max(1, std::min(p.m, h->num_sms * h->sp_per_sm));
   CUDA_TRY(h, cudaMemsetAsync(status, 0, (size_t)p.m * 8, st));
   CUDA_TRY(h, cudaMemsetAsync(&ctr->num_cursor[0], 0, sizeof(int), st));  // the row ticket
-  SinglePassArgs sp{&ctr->num_cursor[0], status, p.Cp, &ctr->nnz_c};
+  SinglePassArgs sp{&ctr->num_cursor[0], status, p.Cp, &ctr->nnz_c, guarded ? &ctr->overflow : nullptr};
   const PBEnt<T> *pb = nullptr;
   int pb_last = 0;
   TRY(pack_b<T>(h, (const T *)Bx, &pb, &pb_last));
@@ -989,6 +994,59 @@ extern "C" int b200sp_spgemm_single_pass(b200sp_handle_t h, int dtype, const voi
   p.nnzC = (int64_t)h->h_counters->nnz_c;
   *nnzC = p.nnzC;
   p.valid = false;  // no row lists exist: a value-only re-run has to go through estimate again
+  return B200SP_OK;
+}
+
+extern "C" int b200sp_spgemm_single_pass_direct(b200sp_handle_t h, int dtype, int64_t m, int64_t k, int64_t n,
+                                                int64_t nnzA, int64_t nnzB, const int32_t *dAp, const int32_t *dAj,
+                                                const void *dAx, const int32_t *dBp, const int32_t *dBj,
+                                                const void *dBx, const void *alpha, int32_t *dCp, int32_t *dCj,
+                                                void *dCx, int64_t capacity, int64_t *nnzC, int64_t *num_products) {
+  if (!h) return B200SP_ERR_INVALID;
+  if (dtype != B200SP_R_32F && dtype != B200SP_R_64F) return fail(h, B200SP_ERR_INVALID, "unsupported dtype %d", dtype);
+  if (!nnzC) return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  *nnzC = 0;
+  if (num_products) *num_products = 0;
+  if (m < 0 || n < 0 || (size_t)n * (dtype == B200SP_R_64F ? 8 : 4) > SMEM_DENSE_MAX)
+    return fail(h, B200SP_ERR_INVALID, "single_pass_direct: an n-column accumulator does not fit shared memory (n = %lld)", (long long)n);
+  if (m * n > (int64_t)INT32_MAX || capacity < m * n)
+    return fail(h, B200SP_ERR_INVALID, "single_pass_direct: capacity %lld is below m * n = %lld (or m * n exceeds int32)",
+                (long long)capacity, (long long)(m * n));
+  DeviceGuard guard(h->device);
+  TRY(spgemm_stage1(h, m, k, n, nnzA, nnzB, dAp, dAj, dBp, dBj, B200SP_ALG_DEFAULT, 0.2f, dCp, true));
+  Plan &p = h->plan;
+  cudaStream_t st = h->stream;
+  if (m == 0) return B200SP_OK;
+  if (nnzA == 0 || nnzB == 0) {  // no products: C is empty
+    CUDA_TRY(h, cudaMemsetAsync(dCp, 0, (size_t)(m + 1) * sizeof(int), st));
+    CUDA_TRY(h, cudaStreamSynchronize(st));
+    return B200SP_OK;
+  }
+  if (!dAx || !dBx || !dCj || !dCx) return fail(h, B200SP_ERR_INVALID, "null pointer argument");
+  // C.indptr of rows without entries is written by the kernel too; rows are all visited
+  cudaEventRecord(h->ev[2], st);
+  int rc = dtype == B200SP_R_32F ? run_single_pass<float>(h, alpha, dAx, dBx, dCj, dCx, true)
+                                 : run_single_pass<double>(h, alpha, dAx, dBx, dCj, dCx, true);
+  cudaEventRecord(h->ev[3], st);
+  if (rc != B200SP_OK) return rc;
+  Counters *ctr = (Counters *)h->ws.ptr;
+  CUDA_TRY(h, cudaMemcpyAsync(h->h_counters, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(h, cudaStreamSynchronize(st));
+  cudaEventElapsedTime(&h->ms_symbolic, h->ev[0], h->ev[1]);
+  h->numeric_timed = true;
+  if (h->h_counters->overflow)
+    return fail(h, B200SP_ERR_OVERFLOW, "a row of A@B has more than 2^31-1 intermediate products");
+  if (h->h_counters->b_bad)
+    return fail(h, B200SP_ERR_INVALID,
+                "B is not canonical (a row has unsorted, duplicate or out-of-range column indices): "
+                "canonicalise it first (b200sp_csr_sum_duplicates / b200sp_csr_sort_indices)");
+  p.num_products = (int64_t)h->h_counters->total_products;
+  p.max_row_products = h->h_counters->max_row_products;
+  p.nnz_bound = (int64_t)h->h_counters->total_ub;
+  p.nnzC = (int64_t)h->h_counters->nnz_c;
+  if (num_products) *num_products = p.num_products;
+  *nnzC = p.nnzC;
+  p.valid = false;
   return B200SP_OK;
 }
 

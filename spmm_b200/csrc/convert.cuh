@@ -221,6 +221,98 @@ __global__ void __launch_bounds__(256) k_keys_from_compressed(int nmajor, int nm
   if (__any_sync(FULL, b) && lane == 0) atomicExch(bad, 1);
 }
 
+// ------------------------------------------------------------------ COO -> CSR by row buckets
+// For inputs whose rows are short (the reference's matrices: C2 holds 10.5 entries per row) the five
+// LSD passes over (row, column) keys are mostly wasted motion: a row histogram + scan gives every row
+// its segment, the entries are dropped into their row's segment in whatever order the atomics decide,
+// and each segment is then sorted on (column, input position) - which is a total order, so the result
+// does not depend on the order of arrival, and duplicates end up in input order as the summation
+// rule requires.  Rows longer than COO_ROW_CAP take the radix path (the host decides from the longest
+// row).
+constexpr int COO_ROW_CAP = 512;  // 8 warps x 512 keys x 8 bytes = 32 KB of static shared memory
+
+__global__ void __launch_bounds__(256) k_coo_row_count(long long nnz, int m, int n, const int *__restrict__ row,
+                                                        const int *__restrict__ col, int *__restrict__ cnt,
+                                                        int *__restrict__ bad) {
+  int b = 0;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += (long long)gridDim.x * blockDim.x) {
+    const int r = row[i], c = col[i];
+    if (r < 0 || r >= m || c < 0 || c >= n) b = 1;
+    else atomicAdd(cnt + r, 1);
+  }
+  if (__any_sync(FULL, b) && lane_id() == 0) atomicExch(bad, 1);
+}
+
+// keyc[pos] = column << 32 | input position, pos drawn from the row's cursor (rows with a bad
+// coordinate were not counted and are skipped here as well).
+__global__ void __launch_bounds__(256) k_coo_bucket(long long nnz, int m, int n, const int *__restrict__ row,
+                                                     const int *__restrict__ col, int *__restrict__ cursor,
+                                                     u64 *__restrict__ keyc) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += (long long)gridDim.x * blockDim.x) {
+    const int r = row[i], c = col[i];
+    if (r < 0 || r >= m || c < 0 || c >= n) continue;
+    const int pos = atomicAdd(cursor + r, 1);
+    keyc[pos] = ((u64)(unsigned)c << 32) | (unsigned)i;
+  }
+}
+
+// Warp per row: sorts the row's (column, position) keys and writes the (row, column) keys and the
+// positions in the layout the duplicate summation expects.  Rows of up to 32 entries are sorted in
+// registers (bitonic network over the lanes); longer ones (<= COO_ROW_CAP) in the warp's slice of
+// shared memory.
+__global__ void __launch_bounds__(256) k_coo_sort_rows(int m, const int *__restrict__ rowptr, const u64 *__restrict__ keyc,
+                                                        u64 *__restrict__ keys, int *__restrict__ perm) {
+  __shared__ u64 s_keys[8][COO_ROW_CAP];
+  const int lane = lane_id(), w = threadIdx.x >> 5;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < m; r += warps) {
+    const int b = __ldg(rowptr + r), len = __ldg(rowptr + r + 1) - b;
+    if (len <= 0) continue;
+    const u64 hi = (u64)(unsigned)r << 32;
+    if (len <= 32) {
+      u64 key = lane < len ? keyc[b + lane] : ~0ull;
+#pragma unroll
+      for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          const u64 other = __shfl_xor_sync(FULL, key, j);
+          const bool up = (lane & k) == 0, lower = (lane & j) == 0;
+          const u64 lo_ = key < other ? key : other, hi_ = key < other ? other : key;
+          key = (lower == up) ? lo_ : hi_;
+        }
+      }
+      if (lane < len) {
+        keys[b + lane] = hi | (key >> 32);
+        perm[b + lane] = (int)(unsigned)key;
+      }
+    } else {
+      u64 *sk = s_keys[w];
+      const int P = next_pow2(len);
+      for (int t = lane; t < P; t += 32) sk[t] = t < len ? keyc[b + t] : ~0ull;
+      __syncwarp();
+      for (int k = 2; k <= P; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          for (int t = lane; t < P; t += 32) {
+            const int u = t ^ j;
+            if (u > t) {
+              const u64 x = sk[t], y = sk[u];
+              const bool up = (t & k) == 0;
+              if ((x > y) == up) sk[t] = y, sk[u] = x;
+            }
+          }
+          __syncwarp();
+        }
+      }
+      for (int t = lane; t < len; t += 32) {
+        const u64 key = sk[t];
+        keys[b + t] = hi | (key >> 32);
+        perm[b + t] = (int)(unsigned)key;
+      }
+      __syncwarp();
+    }
+  }
+}
+
 // ------------------------------------------------------------------ outputs from sorted keys
 // ptr_out[s] = first position of a key whose major (high word) is >= s, for s in [0, nmajor];
 // *n_dev (when given) overrides n: the number of keys is only known on the device after the

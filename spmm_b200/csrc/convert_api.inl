@@ -18,12 +18,14 @@ struct SortScratch {
   int *sums;       // tile sums of the generic scan
   long long *total;  // device scalar
   int *flag;         // device scalar
+  int *rowtmp;       // extra_rows ints (row cursors of the bucket path), or null
   int ntiles;
 };
 
-int carve_sort_scratch(b200sp_context *h, int64_t nnz, SortScratch &s) {
+int carve_sort_scratch(b200sp_context *h, int64_t nnz, SortScratch &s, int64_t extra_rows = 0) {
   const size_t ntiles = (size_t)((nnz + RS_TILE - 1) / RS_TILE);
-  const size_t counters = std::max<size_t>(256 * ntiles, (size_t)((nnz + GS_TILE - 1) / GS_TILE) + 1);
+  const size_t counters = std::max<size_t>(std::max<size_t>(256 * ntiles, (size_t)((nnz + GS_TILE - 1) / GS_TILE) + 1),
+                                           (size_t)extra_rows);
   const size_t nsums = (counters + GS_TILE - 1) / GS_TILE + 1;
   const size_t o_k1 = align_up((size_t)nnz * 8, 256);
   const size_t o_p0 = 2 * o_k1;
@@ -31,7 +33,8 @@ int carve_sort_scratch(b200sp_context *h, int64_t nnz, SortScratch &s) {
   const size_t o_c = o_p1 + align_up((size_t)nnz * 4, 256);
   const size_t o_s = o_c + align_up(counters * 4, 256);
   const size_t o_t = o_s + align_up(nsums * 4, 256);
-  TRY(ensure(h, h->ws2, o_t + 256));
+  const size_t o_r = o_t + 256;
+  TRY(ensure(h, h->ws2, o_r + align_up((size_t)extra_rows * 4, 256)));
   char *base = (char *)h->ws2.ptr;
   s.keys[0] = (u64 *)base;
   s.keys[1] = (u64 *)(base + o_k1);
@@ -41,6 +44,7 @@ int carve_sort_scratch(b200sp_context *h, int64_t nnz, SortScratch &s) {
   s.sums = (int *)(base + o_s);
   s.total = (long long *)(base + o_t);
   s.flag = (int *)(base + o_t + 8);
+  s.rowtmp = extra_rows ? (int *)(base + o_r) : nullptr;
   s.ntiles = (int)ntiles;
   return B200SP_OK;
 }
@@ -117,8 +121,31 @@ template <typename T>
 int run_coo_to_csr(b200sp_context *h, int64_t m, int64_t n, int64_t nnz, const int *row, const int *col, const T *val,
                    int *Cp, int *Cj, T *Cx, int64_t *nnz_out) {
   SortScratch s;
-  TRY(carve_sort_scratch(h, nnz, s));
-  CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, sizeof(int), h->stream));
+  TRY(carve_sort_scratch(h, nnz, s, m + 1));
+  cudaStream_t st = h->stream;
+  CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, 2 * sizeof(int), st));  // [bad coordinate | longest row]
+  // ---- row buckets: histogram -> scan -> drop into the row's segment -> in-row sort (convert.cuh) ----
+  const char *force = getenv("B200SP_COO_PATH");  // radix | bucket (tests / measurements)
+  if (!(force && strcmp(force, "radix") == 0)) {
+    CUDA_TRY(h, cudaMemsetAsync(Cp, 0, (size_t)(m + 1) * sizeof(int), st));
+    k_coo_row_count<<<flat_grid(h, nnz, 1024), 256, 0, st>>>(nnz, (int)m, (int)n, row, col, Cp, s.flag);
+    TRY(check_launch(h, "k_coo_row_count"));
+    TRY(dev_exscan(h, Cp, m + 1, s.sums, nullptr));
+    k_max_row_len<<<flat_grid(h, m, 256), 256, 0, st>>>((int)m, Cp, s.flag + 1);
+    TRY(check_launch(h, "k_max_row_len"));
+    int head[2] = {0, 0};
+    CUDA_TRY(h, cudaMemcpyAsync(head, s.flag, sizeof(head), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(h, cudaStreamSynchronize(st));
+    if (head[0]) return fail(h, B200SP_ERR_INVALID, "coo_to_csr: index out of range or malformed pointer array");
+    if (head[1] <= COO_ROW_CAP) {
+      CUDA_TRY(h, cudaMemcpyAsync(s.rowtmp, Cp, (size_t)m * sizeof(int), cudaMemcpyDeviceToDevice, st));
+      k_coo_bucket<<<flat_grid(h, nnz, 1024), 256, 0, st>>>(nnz, (int)m, (int)n, row, col, s.rowtmp, s.keys[1]);
+      TRY(check_launch(h, "k_coo_bucket"));
+      k_coo_sort_rows<<<flat_grid(h, m, 8), 256, 0, st>>>((int)m, Cp, s.keys[1], s.keys[0], s.perm[0]);
+      TRY(check_launch(h, "k_coo_sort_rows"));
+      return finish_unique<T>(h, s, 0, m, nnz, val, Cp, Cj, Cx, nnz_out, "coo_to_csr");
+    }
+  }
   k_keys_from_coo<<<flat_grid(h, nnz, 1024), 256, 0, h->stream>>>(nnz, (int)m, (int)n, row, col, s.keys[0], s.flag);
   TRY(check_launch(h, "k_keys_from_coo"));
   int cur = 0;

@@ -705,6 +705,8 @@ struct SinglePassArgs {
   unsigned long long *status;   // m words, zeroed before the launch: flag << 62 | value
   int *Cp;                      // m + 1 row pointers, written here
   unsigned long long *nnz_out;  // total, written by the last row
+  const int *guard;             // optional: two flags (row-product overflow, B not canonical) set by the estimate
+                                // kernels in front of this launch; the kernel does nothing when either is set
 };
 #define SP_FLAG_AGG (1ull << 62)
 #define SP_FLAG_PREFIX (2ull << 62)
@@ -758,6 +760,7 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
   const int NT = blockDim.x, tid = threadIdx.x, lane = lane_id(), w = tid >> 5, nw = NT >> 5;
   const T UNT = NegZero<T>::value();
   const int npad = (n + 127) & ~127;
+  if (SINGLE && sp.guard && (sp.guard[0] | sp.guard[1])) return;  // grid-uniform
   for (int c = tid; c < npad; c += NT) acc[c] = UNT;
   // columns per warp for the output sweep, a multiple of 128
   const int cpw = ((npad + nw - 1) / nw + 127) & ~127;

@@ -97,6 +97,47 @@ class SpgemmPlan:
         return c
 
 
+_DIRECT_MAX_BYTES = 4 << 30  # C allocated at m * n entries: only while that stays small
+
+
+def _spgemm_direct(a, b, alpha):
+    """b200sp_spgemm_single_pass_direct when the sizes alone say C will be well filled: expected
+    products nnzA * nnzB / k >= m * n / 2, an n-column accumulator fits shared memory and m * n entries
+    of C are affordable.  No host synchronisation before the kernel (the estimate's costs ~45 us of a
+    1.25 ms product on C3).  Returns None when it does not apply."""
+    import os
+    m, k = a.shape
+    _, n = b.shape
+    if os.environ.get("B200SP_SINGLE_PASS") == "0" or os.environ.get("B200SP_SINGLE_PASS_DIRECT") == "0":
+        return None
+    a, b = _cast_common_type(a, b)
+    s = a.data.element_size()
+    if not (m > 0 and k > 0 and n * s <= 208 * 1024 and m * n <= 2 ** 31 - 1 and m * n * (4 + s) <= _DIRECT_MAX_BYTES
+            and a.nnz * (b.nnz / k) >= 0.5 * m * n):
+        return None
+    dev, dt = a.device, a.dtype
+    lib = _lib.load()
+    h = _lib.handle(dev.index)
+    _bind_stream(h, dev)
+    cap = m * n
+    try:
+        indptr = torch.empty(m + 1, dtype=torch.int32, device=dev)
+        c_indices = torch.empty(cap, dtype=torch.int32, device=dev)
+        c_data = torch.empty(cap, dtype=_TORCH_DT[dt], device=dev)
+    except torch.OutOfMemoryError as e:
+        raise MemoryError(str(e)) from e
+    _abuf, aptr = _scalar(alpha, dt)
+    c_nnz, prods = ctypes.c_int64(0), ctypes.c_int64(0)
+    _lib.check(h, lib.b200sp_spgemm_single_pass_direct(
+        h, _dt_code(dt), m, k, n, a.nnz, b.nnz, a.indptr.data_ptr(), a.indices.data_ptr(), a.data.data_ptr(),
+        b.indptr.data_ptr(), b.indices.data_ptr(), b.data.data_ptr(), aptr, indptr.data_ptr(), c_indices.data_ptr(),
+        c_data.data_ptr(), cap, ctypes.byref(c_nnz), ctypes.byref(prods)))
+    nnz = int(c_nnz.value)
+    c = csr_matrix((c_data[:nnz], c_indices[:nnz], indptr), shape=(m, n))
+    c._canonical = True
+    return c
+
+
 def _spgemm_single_pass(a, b, alpha):
     """b200sp_spgemm_estimate, then b200sp_spgemm_single_pass when the library chooses it.
     Returns the product, or (a, b, indptr) for the two-pass plan to continue from the estimate."""
@@ -160,6 +201,9 @@ def spgemm(a, b, alpha=1, alg=0, chunk_fraction=0.2, verbose=False):
         # default mode: products per row first; well-filled C takes the single-pass kernel (C.indices /
         # C.data allocated at the bound sum_i min(products_i, n), trimmed to views of nnz(C) entries -
         # the memory-for-time trade of cuSPARSE's ALG1); anything else continues with the two-pass plan
+        c = _spgemm_direct(a, b, alpha)
+        if c is not None:
+            return c
         c = _spgemm_single_pass(a, b, alpha)
         if isinstance(c, csr_matrix):
             return c

@@ -43,6 +43,20 @@ def test_coo_to_csr_bitwise(m, n, k, kind, dt):
         helpers.assert_csr_bitwise(_csr_np(got), (M.indptr, M.indices, M.data), "vs scipy")
 
 
+@pytest.mark.parametrize("path", ["radix", "bucket"])
+def test_coo_to_csr_both_paths(path, monkeypatch):
+    """COO -> CSR has two device paths - row buckets + in-row sort (short rows) and the LSD radix sort over
+    (row, column) keys (any row length; also the fallback of the first) - with the same contract."""
+    import spmm_b200
+    monkeypatch.setenv("B200SP_COO_PATH", path)
+    for (m, n, k, kind) in [(64, 64, 900, "pairs"), (200, 150, 50000, "heavy"), (70000, 70000, 300000, "heavy"),
+                            (3000, 7, 4000, "pairs"), (1, 5000, 20000, "heavy"), (40, 3000, 30000, "heavy")]:
+        gen = helpers.coo_with_pairs if kind == "pairs" else helpers.coo_heavy_duplicates
+        row, col, val = gen(m, n, k, 23, np.float32)
+        got = spmm_b200.coo_matrix((val, (row, col)), shape=(m, n)).tocsr()
+        helpers.assert_csr_bitwise(_csr_np(got), oracle.coo_to_csr(row, col, val, (m, n)), f"coo {path} {m}x{n} {kind}")
+
+
 def test_coo_long_duplicate_run_and_determinism():
     import spmm_b200
     rng = np.random.default_rng(5)

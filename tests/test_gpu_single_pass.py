@@ -51,8 +51,14 @@ def test_well_filled_products_take_the_single_pass(b200, n, d, dtype, monkeypatc
     A = helpers.profiler_matrix(m, n, d, seed=n, dtype=dtype)
     B = helpers.profiler_matrix(n, n, d, seed=n + 1, dtype=dtype)
     got, nl = launches_of(b200, lambda: dev_spgemm(b200, A, B))
-    assert nl == 5, f"{nl} kernels: not the single-pass path (k_row_products, canonical check, scatter, k_pack_b, dense)"
+    # the sizes alone say "well filled" here, so the operator takes the direct form: no row lists, no host
+    # synchronisation before the kernel (k_row_products, canonical check, k_pack_b, dense)
+    assert nl == 4, f"{nl} kernels: not b200sp_spgemm_single_pass_direct"
     want = oracle_spgemm(A, B)
+    assert_csr_bitwise(got, want, f"single pass direct n={n} d={d}")
+    monkeypatch.setenv("B200SP_SINGLE_PASS_DIRECT", "0")
+    got, nl = launches_of(b200, lambda: dev_spgemm(b200, A, B))
+    assert nl == 5, f"{nl} kernels: not estimate + single pass (k_row_products, canonical check, scatter, k_pack_b, dense)"
     assert_csr_bitwise(got, want, f"single pass n={n} d={d}")
     monkeypatch.setenv("B200SP_SINGLE_PASS", "0")
     two, nl2 = launches_of(b200, lambda: dev_spgemm(b200, A, B))
@@ -86,14 +92,23 @@ def ragged_pair(dtype, seed=5, m=6000, k=900, n=1500):
 @pytest.mark.parametrize("alpha", [1, -0.75])
 def test_forced_single_pass_ragged_rows(b200, dtype, alpha, monkeypatch):
     monkeypatch.setenv("B200SP_SINGLE_PASS_RATIO", "0")
+    monkeypatch.setenv("B200SP_SINGLE_PASS_DIRECT", "0")
     A, B = ragged_pair(dtype)
+    want = oracle_spgemm(A, B, alpha=alpha)
     got, nl = launches_of(b200, lambda: dev_spgemm(b200, A, B, alpha=alpha))
     assert nl == 5
-    assert_csr_bitwise(got, oracle_spgemm(A, B, alpha=alpha), f"ragged alpha={alpha}")
+    assert_csr_bitwise(got, want, f"ragged alpha={alpha}")
+    # the direct form on the same ragged input (capacity m * n, no estimate): called through the C ABI by the
+    # operator whenever the sizes say so; here it is made to by the sizes of this pair
+    monkeypatch.delenv("B200SP_SINGLE_PASS_DIRECT")
+    got, nl = launches_of(b200, lambda: dev_spgemm(b200, A, B, alpha=alpha))
+    assert nl in (4, 5)
+    assert_csr_bitwise(got, want, f"ragged direct alpha={alpha}")
 
 
 def test_forced_single_pass_grid_and_empty(b200, monkeypatch):
     monkeypatch.setenv("B200SP_SINGLE_PASS_RATIO", "0")
+    monkeypatch.setenv("B200SP_SINGLE_PASS_DIRECT", "0")
     for n in (32, 256, 1024):
         for d in (0.01, 0.3):
             A, B = helpers.grid_case(n, d)
@@ -114,7 +129,7 @@ def test_many_rows_deterministic(b200, monkeypatch):
     A = helpers.profiler_matrix(40000, 1024, 0.03, seed=9)
     B = helpers.profiler_matrix(1024, 1024, 0.03, seed=10)
     got, nl = launches_of(b200, lambda: dev_spgemm(b200, A, B))
-    assert nl == 5
+    assert nl in (4, 5)
     assert_csr_bitwise(got, oracle_spgemm(A, B), "many rows")
     again = dev_spgemm(b200, A, B)
     assert_csr_bitwise(again, got, "second run")
@@ -179,3 +194,48 @@ def test_c_abi_estimate_contract(b200):
         assert single.value == 0
     finally:
         lib.b200sp_destroy(h)
+
+
+def test_direct_entry_contract(b200):
+    """b200sp_spgemm_single_pass_direct through the C ABI: result, products, untouched tail, capacity below
+    m * n refused, non-canonical B reported after the (skipped) kernel with nothing written."""
+    from spmm_b200 import _lib as L
+    lib = L.load()
+    h = L.new_handle(0)
+    try:
+        A = helpers.profiler_matrix(300, 1024, 0.05, seed=3, dtype=np.float64)
+        B = helpers.profiler_matrix(1024, 900, 0.05, seed=4, dtype=np.float64)
+        want = oracle_spgemm(A, B, alpha=-2.0)
+        t = lambda x, dt: torch.from_numpy(np.ascontiguousarray(x)).to("cuda", dt)
+        ap, aj, ax = t(A.indptr, torch.int32), t(A.indices, torch.int32), t(A.data, torch.float64)
+        bp, bj, bx = t(B.indptr, torch.int32), t(B.indices, torch.int32), t(B.data, torch.float64)
+        m, k, n = A.shape[0], A.shape[1], B.shape[1]
+        cap = m * n
+        cp = torch.empty(m + 1, dtype=torch.int32, device="cuda")
+        cj = torch.full((cap,), -7, dtype=torch.int32, device="cuda")
+        cx = torch.full((cap,), float("nan"), dtype=torch.float64, device="cuda")
+        P = lambda x: ctypes.c_void_p(x.data_ptr())
+        nnz, prods = ctypes.c_int64(), ctypes.c_int64()
+        alpha = ctypes.c_double(-2.0)
+
+        def call(bj_, capacity):
+            return lib.b200sp_spgemm_single_pass_direct(h, L.R_64F, m, k, n, A.nnz, B.nnz, P(ap), P(aj), P(ax), P(bp), P(bj_), P(bx),
+                                                        ctypes.byref(alpha), P(cp), P(cj), P(cx), capacity, ctypes.byref(nnz),
+                                                        ctypes.byref(prods))
+        assert call(bj, cap - 1) == L.ERR_INVALID
+        bad = bj.clone()
+        r = int(np.flatnonzero(np.diff(B.indptr) >= 2)[0])
+        s0 = int(B.indptr[r])
+        bad[s0], bad[s0 + 1] = bj[s0 + 1].item(), bj[s0].item()  # one unsorted row
+        assert call(bad, cap) == L.ERR_INVALID and b"not canonical" in lib.b200sp_last_error(h)
+        torch.cuda.synchronize()
+        assert bool((cj == -7).all()), "the kernel ran on a non-canonical B"
+        L.check(h, call(bj, cap))
+        torch.cuda.synchronize()
+        kk = nnz.value
+        assert prods.value == int((A.astype(bool).astype(np.int64) @ np.diff(B.indptr)).sum())
+        assert_csr_bitwise((cp.cpu().numpy(), cj[:kk].cpu().numpy(), cx[:kk].cpu().numpy()), want, "direct via C ABI")
+        assert bool((cj[kk:] == -7).all()) and bool(torch.isnan(cx[kk:]).all())
+    finally:
+        lib.b200sp_destroy(h)
+
