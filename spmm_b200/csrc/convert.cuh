@@ -256,60 +256,168 @@ __global__ void __launch_bounds__(256) k_coo_bucket(long long nnz, int m, int n,
   }
 }
 
-// Warp per row: sorts the row's (column, position) keys and writes the (row, column) keys and the
-// positions in the layout the duplicate summation expects.  Rows of up to 32 entries are sorted in
-// registers (bitonic network over the lanes); longer ones (<= COO_ROW_CAP) in the warp's slice of
+// Bitonic network over the G lanes of a subgroup (G = 16 or 32), ascending; `sl` = lane inside the subgroup.
+template <int G>
+__device__ __forceinline__ u64 subgroup_sort(u64 key, int sl) {
+#pragma unroll
+  for (int k = 2; k <= G; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      const u64 other = __shfl_xor_sync(FULL, key, j);  // j < G: the partner is in the same subgroup
+      const bool up = (sl & k) == 0, lower = (sl & j) == 0;
+      const u64 lo_ = key < other ? key : other, hi_ = key < other ? other : key;
+      key = (lower == up) ? lo_ : hi_;
+    }
+  }
+  return key;
+}
+
+// Sorts every row's (column, position) keys in place (keyc) and counts its distinct columns (ucnt[r];
+// ucnt[m] is left alone).  A warp takes two neighbouring rows at a time: both of at most 16 entries -
+// the common case on the reference's matrices - are sorted side by side in the two half warps; rows of up
+// to 32 entries by the whole warp in registers, longer ones (<= COO_ROW_CAP) in the warp's slice of
 // shared memory.
-__global__ void __launch_bounds__(256) k_coo_sort_rows(int m, const int *__restrict__ rowptr, const u64 *__restrict__ keyc,
-                                                        u64 *__restrict__ keys, int *__restrict__ perm) {
+__global__ void __launch_bounds__(256) k_coo_sort_rows(int m, const int *__restrict__ rowptr, u64 *__restrict__ keyc,
+                                                        int *__restrict__ ucnt) {
   __shared__ u64 s_keys[8][COO_ROW_CAP];
   const int lane = lane_id(), w = threadIdx.x >> 5;
   const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int r0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 2; r0 < m; r0 += warps * 2) {
+    const int b0 = __ldg(rowptr + r0), b1 = __ldg(rowptr + r0 + 1);
+    const int b2 = r0 + 1 < m ? __ldg(rowptr + r0 + 2) : b1;
+    const int len0 = b1 - b0, len1 = b2 - b1;
+    if (len0 <= 16 && len1 <= 16) {
+      const int sg = lane >> 4, sl = lane & 15;
+      const int b = sg ? b1 : b0, len = sg ? len1 : len0;
+      u64 key = sl < len ? keyc[b + sl] : ~0ull;
+      key = subgroup_sort<16>(key, sl);
+      const u64 prev = __shfl_up_sync(FULL, key, 1);
+      const bool head = sl < len && (sl == 0 || (prev >> 32) != (key >> 32));
+      const unsigned heads = __ballot_sync(FULL, head);
+      if (sl < len) keyc[b + sl] = key;
+      if (lane == 0) ucnt[r0] = __popc(heads & 0xffffu);
+      if (lane == 16 && r0 + 1 < m) ucnt[r0 + 1] = __popc(heads >> 16);
+      continue;
+    }
+    for (int q = 0; q < 2 && r0 + q < m; ++q) {
+      const int b = q ? b1 : b0, len = q ? len1 : len0;
+      if (len <= 32) {
+        u64 key = lane < len ? keyc[b + lane] : ~0ull;
+        key = subgroup_sort<32>(key, lane);
+        const u64 prev = __shfl_up_sync(FULL, key, 1);
+        const bool head = lane < len && (lane == 0 || (prev >> 32) != (key >> 32));
+        const unsigned heads = __ballot_sync(FULL, head);
+        if (lane < len) keyc[b + lane] = key;
+        if (lane == 0) ucnt[r0 + q] = __popc(heads);
+      } else {
+        u64 *sk = s_keys[w];
+        const int P = next_pow2(len);
+        for (int t = lane; t < P; t += 32) sk[t] = t < len ? keyc[b + t] : ~0ull;
+        __syncwarp();
+        for (int k = 2; k <= P; k <<= 1) {
+          for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = lane; t < P; t += 32) {
+              const int u = t ^ j;
+              if (u > t) {
+                const u64 x = sk[t], y = sk[u];
+                const bool up = (t & k) == 0;
+                if ((x > y) == up) sk[t] = y, sk[u] = x;
+              }
+            }
+            __syncwarp();
+          }
+        }
+        int heads = 0;
+        for (int t = lane; t < len; t += 32) {
+          const u64 key = sk[t];
+          keyc[b + t] = key;
+          heads += (t == 0 || (sk[t - 1] >> 32) != (key >> 32));
+        }
+        heads = warp_sum(heads);
+        if (lane == 0) ucnt[r0 + q] = heads;
+        __syncwarp();
+      }
+    }
+  }
+}
+
+// Warp per row: the row's sorted (column, position) keys -> its distinct columns and their sums (the
+// duplicates of a column are neighbours, in input order, and are added sequentially with separately
+// rounded adds), written at Cp[r] (the scanned distinct-column counts).
+template <typename T>
+__global__ void __launch_bounds__(256) k_coo_emit_rows(int m, const int *__restrict__ rowptr, const u64 *__restrict__ keyc,
+                                                        const T *__restrict__ val, const int *__restrict__ Cp,
+                                                        int *__restrict__ Cj, T *__restrict__ Cx) {
+  const int lane = lane_id();
+  const int warps = (gridDim.x * blockDim.x) >> 5;
   for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < m; r += warps) {
     const int b = __ldg(rowptr + r), len = __ldg(rowptr + r + 1) - b;
-    if (len <= 0) continue;
-    const u64 hi = (u64)(unsigned)r << 32;
-    if (len <= 32) {
-      u64 key = lane < len ? keyc[b + lane] : ~0ull;
-#pragma unroll
-      for (int k = 2; k <= 32; k <<= 1) {
-#pragma unroll
-        for (int j = k >> 1; j > 0; j >>= 1) {
-          const u64 other = __shfl_xor_sync(FULL, key, j);
-          const bool up = (lane & k) == 0, lower = (lane & j) == 0;
-          const u64 lo_ = key < other ? key : other, hi_ = key < other ? other : key;
-          key = (lower == up) ? lo_ : hi_;
+    int out = __ldg(Cp + r);
+    for (int t0 = 0; t0 < len; t0 += 32) {
+      const int t = t0 + lane;
+      const bool in = t < len;
+      const u64 key = in ? keyc[b + t] : ~0ull;
+      const int col = (int)(key >> 32);
+      const bool head = in && (t == 0 || (int)(keyc[b + t - 1] >> 32) != col);
+      const unsigned heads = __ballot_sync(FULL, head);
+      if (head) {
+        T sum = val[(unsigned)key];
+        for (int e = t + 1; e < len; ++e) {  // the rest of the run (usually empty)
+          const u64 k2 = keyc[b + e];
+          if ((int)(k2 >> 32) != col) break;
+          sum = add_rn(sum, val[(unsigned)k2]);
         }
+        const int o = out + __popc(heads & ((1u << lane) - 1u));
+        Cj[o] = col;
+        Cx[o] = sum;
       }
-      if (lane < len) {
-        keys[b + lane] = hi | (key >> 32);
-        perm[b + lane] = (int)(unsigned)key;
-      }
-    } else {
-      u64 *sk = s_keys[w];
-      const int P = next_pow2(len);
-      for (int t = lane; t < P; t += 32) sk[t] = t < len ? keyc[b + t] : ~0ull;
-      __syncwarp();
-      for (int k = 2; k <= P; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-          for (int t = lane; t < P; t += 32) {
-            const int u = t ^ j;
-            if (u > t) {
-              const u64 x = sk[t], y = sk[u];
-              const bool up = (t & k) == 0;
-              if ((x > y) == up) sk[t] = y, sk[u] = x;
-            }
-          }
-          __syncwarp();
-        }
-      }
-      for (int t = lane; t < len; t += 32) {
-        const u64 key = sk[t];
-        keys[b + t] = hi | (key >> 32);
-        perm[b + t] = (int)(unsigned)key;
-      }
-      __syncwarp();
+      out += __popc(heads);
     }
+  }
+}
+
+// Transposition (CSC <-> CSR) by the same buckets: count the entries of every minor index, scan, drop
+// (major, position) keys into the minor's segment, sort the segments (k_coo_sort_rows), write out.
+__global__ void __launch_bounds__(256) k_count_minor(long long nnz, int nminor, const int *__restrict__ idx,
+                                                      int *__restrict__ cnt, int *__restrict__ bad) {
+  int b = 0;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += (long long)gridDim.x * blockDim.x) {
+    const int j = idx[i];
+    if (j < 0 || j >= nminor) b = 1;
+    else atomicAdd(cnt + j, 1);
+  }
+  if (__any_sync(FULL, b) && lane_id() == 0) atomicExch(bad, 1);
+}
+
+__global__ void __launch_bounds__(256) k_bucket_compressed(int nmajor, int nminor, long long nnz, const int *__restrict__ ptr,
+                                                            const int *__restrict__ idx, int *__restrict__ cursor,
+                                                            u64 *__restrict__ keyc, int *__restrict__ bad) {
+  const int lane = lane_id();
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  int b = 0;
+  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < nmajor; s += warps) {
+    const int t0 = ptr[s], t1 = ptr[s + 1];
+    if (t0 < 0 || t1 < t0 || t1 > nnz || (s == 0 && t0 != 0) || (s == nmajor - 1 && t1 != nnz)) {
+      b = 1;
+      continue;
+    }
+    for (int t = t0 + lane; t < t1; t += 32) {
+      const int j = idx[t];
+      if (j < 0 || j >= nminor) continue;  // flagged by k_count_minor
+      const int pos = atomicAdd(cursor + j, 1);
+      keyc[pos] = ((u64)(unsigned)s << 32) | (unsigned)t;
+    }
+  }
+  if (__any_sync(FULL, b) && lane == 0) atomicExch(bad, 1);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_emit_bucketed(long long nnz, const u64 *__restrict__ keyc, const T *__restrict__ val,
+                                                        int *__restrict__ idx_out, T *__restrict__ val_out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += (long long)gridDim.x * blockDim.x) {
+    const u64 key = keyc[i];
+    idx_out[i] = (int)(key >> 32);
+    val_out[i] = val[(unsigned)key];
   }
 }
 

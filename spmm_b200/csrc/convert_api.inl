@@ -138,12 +138,24 @@ int run_coo_to_csr(b200sp_context *h, int64_t m, int64_t n, int64_t nnz, const i
     CUDA_TRY(h, cudaStreamSynchronize(st));
     if (head[0]) return fail(h, B200SP_ERR_INVALID, "coo_to_csr: index out of range or malformed pointer array");
     if (head[1] <= COO_ROW_CAP) {
-      CUDA_TRY(h, cudaMemcpyAsync(s.rowtmp, Cp, (size_t)m * sizeof(int), cudaMemcpyDeviceToDevice, st));
-      k_coo_bucket<<<flat_grid(h, nnz, 1024), 256, 0, st>>>(nnz, (int)m, (int)n, row, col, s.rowtmp, s.keys[1]);
+      int *cursor = s.counts;  // >= m + 1 ints (carve_sort_scratch sizes the counters for it), free in this path
+      CUDA_TRY(h, cudaMemcpyAsync(cursor, Cp, (size_t)m * sizeof(int), cudaMemcpyDeviceToDevice, st));
+      k_coo_bucket<<<flat_grid(h, nnz, 1024), 256, 0, st>>>(nnz, (int)m, (int)n, row, col, cursor, s.keys[1]);
       TRY(check_launch(h, "k_coo_bucket"));
-      k_coo_sort_rows<<<flat_grid(h, m, 8), 256, 0, st>>>((int)m, Cp, s.keys[1], s.keys[0], s.perm[0]);
+      // Cp holds the row segments of the un-summed entries until the distinct-column counts are scanned into it
+      int *rowptr = s.rowtmp;
+      CUDA_TRY(h, cudaMemcpyAsync(rowptr, Cp, (size_t)(m + 1) * sizeof(int), cudaMemcpyDeviceToDevice, st));
+      k_coo_sort_rows<<<flat_grid(h, (m + 1) / 2, 8), 256, 0, st>>>((int)m, rowptr, s.keys[1], Cp);
       TRY(check_launch(h, "k_coo_sort_rows"));
-      return finish_unique<T>(h, s, 0, m, nnz, val, Cp, Cj, Cx, nnz_out, "coo_to_csr");
+      CUDA_TRY(h, cudaMemsetAsync(Cp + m, 0, sizeof(int), st));
+      TRY(dev_exscan(h, Cp, m + 1, s.sums, s.total));
+      k_coo_emit_rows<T><<<flat_grid(h, m, 8), 256, 0, st>>>((int)m, rowptr, s.keys[1], val, Cp, Cj, Cx);
+      TRY(check_launch(h, "k_coo_emit_rows"));
+      long long total = 0;
+      CUDA_TRY(h, cudaMemcpyAsync(&total, s.total, sizeof(total), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(h, cudaStreamSynchronize(st));
+      *nnz_out = total;
+      return B200SP_OK;
     }
   }
   k_keys_from_coo<<<flat_grid(h, nnz, 1024), 256, 0, h->stream>>>(nnz, (int)m, (int)n, row, col, s.keys[0], s.flag);
@@ -173,9 +185,38 @@ template <typename T>
 int run_transpose(b200sp_context *h, int64_t nmajor, int64_t nminor, int64_t nnz, const int *ptr, const int *idx,
                   const T *val, int *out_ptr, int *out_idx, T *out_val) {
   SortScratch s;
-  TRY(carve_sort_scratch(h, nnz, s));
+  TRY(carve_sort_scratch(h, nnz, s, nminor + 1));
   cudaStream_t st = h->stream;
-  CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, sizeof(int), st));
+  CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, 2 * sizeof(int), st));  // [bad input | longest output segment]
+  const char *force = getenv("B200SP_COO_PATH");  // radix | bucket: the same switch as COO -> CSR
+  if (!(force && strcmp(force, "radix") == 0)) {
+    // ---- buckets: entries per minor index -> scan -> (major, position) keys dropped into the segment -> in-segment sort
+    CUDA_TRY(h, cudaMemsetAsync(out_ptr, 0, (size_t)(nminor + 1) * sizeof(int), st));
+    k_count_minor<<<flat_grid(h, nnz, 1024), 256, 0, st>>>(nnz, (int)nminor, idx, out_ptr, s.flag);
+    TRY(check_launch(h, "k_count_minor"));
+    TRY(dev_exscan(h, out_ptr, nminor + 1, s.sums, nullptr));
+    k_max_row_len<<<flat_grid(h, nminor, 256), 256, 0, st>>>((int)nminor, out_ptr, s.flag + 1);
+    TRY(check_launch(h, "k_max_row_len"));
+    int head[2] = {0, 0};
+    CUDA_TRY(h, cudaMemcpyAsync(head, s.flag, sizeof(head), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(h, cudaStreamSynchronize(st));
+    if (head[0]) return fail(h, B200SP_ERR_INVALID, "transpose: index out of range or malformed pointer array");
+    if (head[1] <= COO_ROW_CAP) {
+      CUDA_TRY(h, cudaMemcpyAsync(s.rowtmp, out_ptr, (size_t)nminor * sizeof(int), cudaMemcpyDeviceToDevice, st));
+      k_bucket_compressed<<<flat_grid(h, nmajor, 8), 256, 0, st>>>((int)nmajor, (int)nminor, nnz, ptr, idx, s.rowtmp, s.keys[1], s.flag);
+      TRY(check_launch(h, "k_bucket_compressed"));
+      k_coo_sort_rows<<<flat_grid(h, (nminor + 1) / 2, 8), 256, 0, st>>>((int)nminor, out_ptr, s.keys[1], s.counts);
+      TRY(check_launch(h, "k_coo_sort_rows"));
+      k_emit_bucketed<T><<<flat_grid(h, nnz, 1024), 256, 0, st>>>(nnz, s.keys[1], val, out_idx, out_val);
+      TRY(check_launch(h, "k_emit_bucketed"));
+      int bad2 = 0;
+      CUDA_TRY(h, cudaMemcpyAsync(&bad2, s.flag, sizeof(bad2), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(h, cudaStreamSynchronize(st));
+      if (bad2) return fail(h, B200SP_ERR_INVALID, "transpose: index out of range or malformed pointer array");
+      return B200SP_OK;
+    }
+    CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, 2 * sizeof(int), st));
+  }
   k_keys_from_compressed<false><<<flat_grid(h, nmajor, 8), 256, 0, st>>>((int)nmajor, (int)nminor, nnz, ptr, idx, s.keys[0],
                                                                     s.flag);
   TRY(check_launch(h, "k_keys_from_compressed"));

@@ -55,6 +55,11 @@ def test_coo_to_csr_both_paths(path, monkeypatch):
         row, col, val = gen(m, n, k, 23, np.float32)
         got = spmm_b200.coo_matrix((val, (row, col)), shape=(m, n)).tocsr()
         helpers.assert_csr_bitwise(_csr_np(got), oracle.coo_to_csr(row, col, val, (m, n)), f"coo {path} {m}x{n} {kind}")
+    # the transposition uses the same two paths (a segment of more than COO_ROW_CAP entries falls back to radix)
+    for (m, n, d) in [(300, 200, 0.1), (5000, 40, 0.3), (3, 9000, 0.4), (20000, 20000, 0.0005)]:
+        M = sp.random(m, n, density=d, format="csc", dtype=np.float32, random_state=np.random.RandomState(5))
+        got = spmm_b200.csc_matrix(M).tocsr()
+        helpers.assert_csr_bitwise(_csr_np(got), oracle.transpose_compressed(M.indptr, M.indices, M.data, m), f"csc->csr {path} {m}x{n}")
 
 
 def test_coo_long_duplicate_run_and_determinism():
