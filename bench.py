@@ -515,6 +515,9 @@ def d2h_probe(torch, dist, dev, world, rank, multi):
     per = int(min(1 << 30, max(arena.size // world, 0)) // 4096 * 4096)
     if per < (1 << 20) or not arena.registered:
         return {"skipped": "no registered shared buffer"}
+    arena.register_range(rank * per, per)
+    if arena.unpinned:
+        return {"skipped": "cudaHostRegister failed on this box"}
     buf = torch.empty(per, dtype=torch.uint8, device=dev)
     buf.fill_(rank + 1)
     lib, h = _lib.load(), _lib.handle(dev.index)

@@ -7,6 +7,7 @@
 // latter is the same sync the reference has at cupyx/cusparse.py:2120-2127).
 #include <cuda_runtime.h>
 #include <stdarg.h>
+#include <stddef.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -744,6 +745,7 @@ int spgemm_stage1(b200sp_context *h, int64_t m, int64_t k, int64_t n, int64_t nn
   char *base = (char *)h->ws.ptr;
   Counters *ctr = (Counters *)base;
   int *rowub = (int *)(base + L.o_ub);
+  int *rowprod = (int *)(base + L.o_st);  // products per row; shares the single-pass status area (used after it is dead)
   p.rows_sym = (int *)(base + L.o_rs);
   p.rows_num = (int *)(base + L.o_rn);
 
@@ -754,11 +756,11 @@ int spgemm_stage1(b200sp_context *h, int64_t m, int64_t k, int64_t n, int64_t nn
     const int G = avg <= 2 ? 2 : avg <= 6 ? 4 : avg <= 12 ? 8 : avg <= 24 ? 16 : 32;
     const int grid = std::max(1, std::min((int)((m + 256 / G - 1) / (256 / G)), h->num_sms * 8));
     switch (G) {
-      case 2: k_row_products<2><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
-      case 4: k_row_products<4><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
-      case 8: k_row_products<8><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
-      case 16: k_row_products<16><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
-      default: k_row_products<32><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr); break;
+      case 2: k_row_products<2><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr, rowprod); break;
+      case 4: k_row_products<4><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr, rowprod); break;
+      case 8: k_row_products<8><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr, rowprod); break;
+      case 16: k_row_products<16><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr, rowprod); break;
+      default: k_row_products<32><<<grid, 256, 0, st>>>(p.m, p.n, dAp, dAj, dBp, rowub, dCp, p.sym_limits, ctr, rowprod); break;
     }
     TRY(check_launch(h, "k_row_products"));
   }
@@ -840,6 +842,26 @@ int spgemm_stage2(b200sp_context *h, int64_t *nnzC) {
   cudaEventElapsedTime(&h->ms_symbolic, h->ev[0], h->ev[1]);
   p.nnzC = (int64_t)h->h_counters->nnz_c;
   for (int b = 0; b < p.num_limits.nbins; ++b) p.num_count[b] = h->h_counters->num_count[b];
+  {  // the rows of the last (ticket-scheduled) bin by decreasing work: see k_work_order
+    const int lb = p.num_limits.nbins - 1;
+    const int kind = p.num_bins[lb].kind, cnt = p.num_count[lb];
+    const bool ticketed = kind == NUM_DENSE_BLOCKED || kind == NUM_RANK || kind == NUM_WARP_BLOCKS;
+    if (ticketed && cnt > 2 * h->num_sms && p.max_row_products >= 64 && !getenv("B200SP_NO_HEAVY_FIRST")) {
+      int off_lb = 0;
+      for (int b = 0; b < lb; ++b) off_lb += p.num_count[b];
+      const int *rowprod = (const int *)(base + L.o_st);
+      static_assert(offsetof(Counters, sym_cursor) == offsetof(Counters, sym_count) + 16 * sizeof(int), "hist | cursor");
+      CUDA_TRY(h, cudaMemsetAsync(&ctr->sym_count[0], 0, 32 * sizeof(int), st));  // 16 bucket counts | 16 cursors (both dead by now)
+      int top_log2 = 0;
+      while ((p.max_row_products >> (top_log2 + 1)) > 0) ++top_log2;
+      const int og = std::max(1, std::min((cnt + 255) / 256, h->num_sms * 8));
+      k_work_hist<<<og, 256, 0, st>>>(p.rows_num + off_lb, cnt, rowprod, top_log2, &ctr->sym_count[0]);
+      TRY(check_launch(h, "k_work_hist"));
+      k_work_order<<<og, 256, 0, st>>>(p.rows_num + off_lb, cnt, rowprod, top_log2, &ctr->sym_count[0], &ctr->sym_cursor[0], p.rows_sym);
+      TRY(check_launch(h, "k_work_order"));
+      CUDA_TRY(h, cudaMemcpyAsync(p.rows_num + off_lb, p.rows_sym, (size_t)cnt * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    }
+  }
   *nnzC = p.nnzC;
   if (p.nnzC > INT32_MAX)
     return fail(h, B200SP_ERR_OVERFLOW, "nnz(C) = %lld does not fit the int32 indptr of CSR", (long long)p.nnzC);

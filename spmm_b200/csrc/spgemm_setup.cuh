@@ -45,7 +45,7 @@ template <int G>
 __global__ void __launch_bounds__(256)
 k_row_products(int m, int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
                const int *__restrict__ Bp, int *__restrict__ rowub, int *__restrict__ Cp,
-               BinLimits bl, Counters *ctr) {
+               BinLimits bl, Counters *ctr, int *__restrict__ rowprod = nullptr) {
   __shared__ int s_hist[MAX_BINS];
   __shared__ unsigned long long s_total, s_ub;
   __shared__ int s_max;
@@ -80,6 +80,7 @@ k_row_products(int m, int n, const int *__restrict__ Ap, const int *__restrict__
       const int p = (int)s;
       const int ub = min(p, n);
       rowub[row] = ub;
+      if (rowprod) rowprod[row] = p;
       if (ub == 0) {
         Cp[row] = 0;
       } else {
@@ -314,6 +315,44 @@ __global__ void __launch_bounds__(SCAN_THREADS)
 k_scan_apply(int *Cp, int m, const long long *tile_sums) {
   __shared__ long long s_warp[33];
   scan_tile(Cp, m, blockIdx.x * SCAN_TILE, tile_sums[blockIdx.x], s_warp);
+}
+
+// Rows of a bin ordered by decreasing work: 16 buckets by the power of two of their intermediate products
+// relative to the largest row (bucket 15 = within a factor 2 of it, bucket 0 = 2^15 times lighter or more),
+// heaviest bucket first, arbitrary order inside a bucket.  The heavy-row kernels hand rows out by ticket in
+// list order: a hub row of a power-law matrix is a whole CTA's work for tens of milliseconds (R-MAT scale 20,
+// row 0: ~8e7 products) and must start first, not wherever the scatter happened to put it
+// (longest-processing-time-first; measured R-MAT scale 18 / 20 numeric pass 46.4 / 577 -> 43.5 / 510 ms with
+// two buckets).
+__device__ __forceinline__ int work_bucket(int prod, int top_log2) {
+  const int l = 31 - __clz(max(prod, 1));
+  return max(0, min(15, l - top_log2 + 15));
+}
+__global__ void __launch_bounds__(256)
+k_work_hist(const int *__restrict__ rows, int cnt, const int *__restrict__ rowprod, int top_log2, int *__restrict__ hist) {
+  __shared__ int s_h[16];
+  if (threadIdx.x < 16) s_h[threadIdx.x] = 0;
+  __syncthreads();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < cnt; i += gridDim.x * blockDim.x)
+    atomicAdd(&s_h[work_bucket(rowprod[rows[i]], top_log2)], 1);
+  __syncthreads();
+  if (threadIdx.x < 16 && s_h[threadIdx.x]) atomicAdd(hist + threadIdx.x, s_h[threadIdx.x]);
+}
+__global__ void __launch_bounds__(256)
+k_work_order(const int *__restrict__ rows, int cnt, const int *__restrict__ rowprod, int top_log2,
+             const int *__restrict__ hist, int *__restrict__ cursor, int *__restrict__ out) {
+  __shared__ int s_base[16];
+  if (threadIdx.x < 16) {
+    int base = 0;
+    for (int q = 15; q > (int)threadIdx.x; --q) base += hist[q];  // the heavier buckets come first
+    s_base[threadIdx.x] = base;
+  }
+  __syncthreads();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < cnt; i += gridDim.x * blockDim.x) {
+    const int r = rows[i];
+    const int bk = work_bucket(rowprod[r], top_log2);
+    out[s_base[bk] + atomicAdd(cursor + bk, 1)] = r;
+  }
 }
 
 }  // namespace b200sp

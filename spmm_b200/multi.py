@@ -234,13 +234,50 @@ class HostArena:
 
     def __init__(self):
         self.path, self.mm, self.size, self.base, self.registered, self.owner = None, None, 0, None, False, False
+        self.ranges = []      # page-aligned [start, end) byte ranges this process has page-locked
+        self.unpinned = False  # a registration failed: copies into the buffer are staged by the driver (slow, correct)
+
+    def _unregister_all(self):
+        if self.ranges and self.base is not None:
+            from . import _lib
+            lib = _lib.load()
+            for a, _b in self.ranges:
+                lib.b200sp_host_unregister(self.base.ctypes.data + a)
+        self.ranges = []
+
+    def register_range(self, offset, nbytes):
+        """Page-lock [offset, offset + nbytes) of the buffer for this process (idempotent, cached).  A rank
+        registers only what it writes: the whole buffer in every process does not scale - at 8 ranks
+        cudaHostRegister of the 17 GB C of eight C3 panels failed in all of them."""
+        if not self.registered or nbytes <= 0 or self.unpinned:
+            return
+        a, b = offset // 4096 * 4096, min(self.size, (offset + nbytes + 4095) // 4096 * 4096)
+        for ra, rb in self.ranges:
+            if ra <= a and b <= rb:
+                return
+        # drop cached ranges that overlap the new one (a page cannot be registered twice in one process)
+        from . import _lib
+        lib = _lib.load()
+        keep = []
+        for ra, rb in self.ranges:
+            if rb <= a or b <= ra:
+                keep.append((ra, rb))
+            else:
+                lib.b200sp_host_unregister(self.base.ctypes.data + ra)
+                a, b = min(a, ra), max(b, rb)
+        self.ranges = keep
+        st = lib.b200sp_host_register(self.base.ctypes.data + a, b - a)
+        if st != _lib.OK:
+            import warnings
+            warnings.warn(f"cudaHostRegister of {b - a} bytes of the shared C buffer failed: copying through pageable memory")
+            self.unpinned = True
+            return
+        self.ranges.append((a, b))
 
     def _close(self):
         if self.mm is None:
             return
-        if self.registered:
-            from . import _lib
-            _lib.load().b200sp_host_unregister(self.base.ctypes.data)
+        self._unregister_all()
         self.base = None
         try:
             self.mm.close()
@@ -272,12 +309,8 @@ class HostArena:
             os.close(fd)
         self.size = size
         self.base = np.frombuffer(self.mm, dtype=np.uint8)
-        if register:
-            from . import _lib
-            st = _lib.load().b200sp_host_register(self.base.ctypes.data, size)
-            if st != _lib.OK:
-                raise MemoryError(f"cudaHostRegister of the shared C buffer ({size} bytes) failed")
-            self.registered = True
+        self.registered = bool(register)  # ranges are page-locked on demand (register_range)
+        self.unpinned = False
         dist.barrier()  # everyone has the file open: rank 0 may drop the name
         if self.owner:
             os.unlink(self.path)
@@ -469,6 +502,10 @@ def spgemm_row_panels(A, B, shape, alg=0, chunk_fraction=0.2, alpha=1.0, compute
         if rank == 0:
             ptr[0] = 0
         # ---- value pass + D2H to the sub-panel's offset ------------------------------------
+        for i, (p0, p1) in enumerate(mine):  # page-lock what this rank is about to write (cached across calls)
+            off, cnt = offsets[(rank, i)], int(my_nnz[i])
+            _ARENA.register_range(o_j + off * 4, cnt * 4)
+            _ARENA.register_range(o_x + off * vnp.itemsize, cnt * vnp.itemsize)
         for i, (p0, p1) in enumerate(mine):
             off, cnt = offsets[(rank, i)], int(my_nnz[i])
             cp = eng.finish(i, idx[off:off + cnt], val[off:off + cnt])
