@@ -442,7 +442,7 @@ int persistent_grid(b200sp_context *h, int nrows, size_t smem_bytes) {
   return std::max(1, std::min(nrows, h->num_sms * per_sm));
 }
 
-int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
+int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt, int *ticket = nullptr) {
   Plan &p = h->plan;
   const BinPlan &bp = p.sym_bins[b];
   cudaStream_t st = h->stream;
@@ -468,7 +468,7 @@ int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
       const size_t fbytes = (size_t)((p.n + 3) / 4) * 4;  // one byte flag per column
       if (fbytes <= SMEM_BITMAP_MAX) {
         TRY(set_smem(h, k_sym_flags_cta, fbytes));
-        k_sym_flags_cta<<<persistent_grid(h, cnt, fbytes + 64), 256, fbytes, st>>>(rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp);
+        k_sym_flags_cta<<<persistent_grid(h, cnt, fbytes + 64), 256, fbytes, st>>>(rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp, ticket);
         return check_launch(h, "k_sym_flags_cta");
       }
       if (bytes <= SMEM_BITMAP_MAX) {
@@ -478,14 +478,14 @@ int launch_symbolic_bin(b200sp_context *h, int b, const int *rows, int cnt) {
         const int per_sm = (int)std::max<size_t>(1, SMEM_MAX / (bytes + 64));
         const int nt = per_sm >= 4 ? 256 : per_sm >= 2 ? 512 : 1024;
         k_sym_bitmap_cta<true><<<persistent_grid(h, cnt, bytes + 64), nt, bytes, st>>>(
-            rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp, nullptr);
+            rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp, nullptr, ticket);
         return check_launch(h, "k_sym_bitmap_cta<smem>");
       }
       int grid = std::max(1, std::min(cnt, 2 * h->num_sms / p.num_chunks));
       TRY(ensure(h, h->ws2, (size_t)grid * bytes));
       CUDA_TRY(h, cudaMemsetAsync(h->ws2.ptr, 0, (size_t)grid * bytes, st));
       k_sym_bitmap_cta<false><<<grid, 1024, 0, st>>>(rows, cnt, p.n, p.Ap, p.Aj, p.Bp, p.Bj, p.Cp,
-                                                    (unsigned *)h->ws2.ptr);
+                                                    (unsigned *)h->ws2.ptr, ticket);
       return check_launch(h, "k_sym_bitmap_cta<global>");
     }
   }
@@ -813,7 +813,25 @@ int spgemm_stage2(b200sp_context *h, int64_t *nnzC) {
   int off = 0;
   for (int b = 0; b < p.sym_limits.nbins; ++b) {
     const int cnt = p.sym_count[b];
-    if (cnt > 0) TRY(launch_symbolic_bin(h, b, p.rows_sym + off, cnt));
+    int *ticket = nullptr;
+    // the last bin (the rows with the most products, no upper limit) of a bitmap / flag kernel: rows by
+    // decreasing work, handed out by ticket (see k_work_order)
+    if (b == p.sym_limits.nbins - 1 && p.sym_bins[b].kind == SYM_CTA_BITMAP && cnt > 2 * h->num_sms &&
+        p.max_row_products >= 64 && !getenv("B200SP_NO_HEAVY_FIRST")) {
+      const int *rowprod = (const int *)(base + L.o_st);
+      CUDA_TRY(h, cudaMemsetAsync(&ctr->sym_count[0], 0, 32 * sizeof(int), st));  // host copies were taken at sync #1
+      CUDA_TRY(h, cudaMemsetAsync(&ctr->ticket, 0, sizeof(int), st));
+      int top_log2 = 0;
+      while ((p.max_row_products >> (top_log2 + 1)) > 0) ++top_log2;
+      const int og = std::max(1, std::min((cnt + 255) / 256, h->num_sms * 8));
+      k_work_hist<<<og, 256, 0, st>>>(p.rows_sym + off, cnt, rowprod, top_log2, &ctr->sym_count[0]);
+      TRY(check_launch(h, "k_work_hist"));
+      k_work_order<<<og, 256, 0, st>>>(p.rows_sym + off, cnt, rowprod, top_log2, &ctr->sym_count[0], &ctr->sym_cursor[0], p.rows_num);
+      TRY(check_launch(h, "k_work_order"));
+      CUDA_TRY(h, cudaMemcpyAsync(p.rows_sym + off, p.rows_num, (size_t)cnt * sizeof(int), cudaMemcpyDeviceToDevice, st));
+      ticket = &ctr->ticket;
+    }
+    if (cnt > 0) TRY(launch_symbolic_bin(h, b, p.rows_sym + off, cnt, ticket));
     off += cnt;
   }
   // counts -> indptr

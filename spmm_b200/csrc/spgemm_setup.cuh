@@ -35,6 +35,8 @@ struct Counters {
   int num_count[MAX_BINS];
   int num_cursor[MAX_BINS];
   unsigned long long total_ub;  // sum_i min(products_i, n): an upper bound of nnz(C) (single-pass mode)
+  int ticket;                   // row ticket of the persistent symbolic kernels (zeroed before each launch)
+  int pad_;
 };
 
 // prods[i] = sum over the nonzeros (i,k) of A of nnz(B_k); ub[i] = min(prods[i], n) is the
