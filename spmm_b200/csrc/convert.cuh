@@ -376,6 +376,29 @@ __global__ void __launch_bounds__(256) k_coo_emit_rows(int m, const int *__restr
   }
 }
 
+// CSR with unsorted rows / duplicates -> the (column, position) keys of its entries, in place of the
+// bucket pass (the entries are grouped by row already).  Raises *bad like k_keys_from_compressed.
+__global__ void __launch_bounds__(256) k_keyc_from_csr(int m, int n, long long nnz, const int *__restrict__ Ap,
+                                                        const int *__restrict__ Aj, u64 *__restrict__ keyc,
+                                                        int *__restrict__ bad) {
+  const int lane = lane_id();
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  int b = 0;
+  for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < m; r += warps) {
+    const int t0 = Ap[r], t1 = Ap[r + 1];
+    if (t0 < 0 || t1 < t0 || t1 > nnz || (r == 0 && t0 != 0) || (r == m - 1 && t1 != nnz)) {
+      b = 1;
+      continue;
+    }
+    for (int t = t0 + lane; t < t1; t += 32) {
+      const int j = Aj[t];
+      if (j < 0 || j >= n) b = 1;
+      keyc[t] = ((u64)(unsigned)j << 32) | (unsigned)t;
+    }
+  }
+  if (__any_sync(FULL, b) && lane == 0) atomicExch(bad, 1);
+}
+
 // Transposition (CSC <-> CSR) by the same buckets: count the entries of every minor index, scan, drop
 // (major, position) keys into the minor's segment, sort the segments (k_coo_sort_rows), write out.
 __global__ void __launch_bounds__(256) k_count_minor(long long nnz, int nminor, const int *__restrict__ idx,

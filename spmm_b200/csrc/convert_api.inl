@@ -169,8 +169,35 @@ template <typename T>
 int run_csr_sum_duplicates(b200sp_context *h, int64_t m, int64_t n, int64_t nnz, const int *Ap, const int *Aj,
                            const T *Ax, int *Cp, int *Cj, T *Cx, int64_t *nnz_out) {
   SortScratch s;
-  TRY(carve_sort_scratch(h, nnz, s));
-  CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, sizeof(int), h->stream));
+  TRY(carve_sort_scratch(h, nnz, s, m + 1));
+  cudaStream_t st = h->stream;
+  CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, 2 * sizeof(int), st));
+  const char *force = getenv("B200SP_COO_PATH");
+  if (!(force && strcmp(force, "radix") == 0)) {
+    // short rows: sort every row's (column, position) keys where they lie, then the per-row ordered sums
+    k_max_row_len<<<flat_grid(h, m, 256), 256, 0, st>>>((int)m, Ap, s.flag + 1);
+    TRY(check_launch(h, "k_max_row_len"));
+    k_keyc_from_csr<<<flat_grid(h, m, 8), 256, 0, st>>>((int)m, (int)n, nnz, Ap, Aj, s.keys[1], s.flag);
+    TRY(check_launch(h, "k_keyc_from_csr"));
+    int head[2] = {0, 0};
+    CUDA_TRY(h, cudaMemcpyAsync(head, s.flag, sizeof(head), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(h, cudaStreamSynchronize(st));
+    if (head[0]) return fail(h, B200SP_ERR_INVALID, "csr_sum_duplicates: index out of range or malformed pointer array");
+    if (head[1] <= COO_ROW_CAP) {
+      k_coo_sort_rows<<<flat_grid(h, (m + 1) / 2, 8), 256, 0, st>>>((int)m, Ap, s.keys[1], Cp);
+      TRY(check_launch(h, "k_coo_sort_rows"));
+      CUDA_TRY(h, cudaMemsetAsync(Cp + m, 0, sizeof(int), st));
+      TRY(dev_exscan(h, Cp, m + 1, s.sums, s.total));
+      k_coo_emit_rows<T><<<flat_grid(h, m, 8), 256, 0, st>>>((int)m, Ap, s.keys[1], Ax, Cp, Cj, Cx);
+      TRY(check_launch(h, "k_coo_emit_rows"));
+      long long total = 0;
+      CUDA_TRY(h, cudaMemcpyAsync(&total, s.total, sizeof(total), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(h, cudaStreamSynchronize(st));
+      *nnz_out = total;
+      return B200SP_OK;
+    }
+    CUDA_TRY(h, cudaMemsetAsync(s.flag, 0, 2 * sizeof(int), st));
+  }
   k_keys_from_compressed<true><<<flat_grid(h, m, 8), 256, 0, h->stream>>>((int)m, (int)n, nnz, Ap, Aj, s.keys[0], s.flag);
   TRY(check_launch(h, "k_keys_from_compressed"));
   int cur = 0;

@@ -60,6 +60,16 @@ def test_coo_to_csr_both_paths(path, monkeypatch):
         M = sp.random(m, n, density=d, format="csc", dtype=np.float32, random_state=np.random.RandomState(5))
         got = spmm_b200.csc_matrix(M).tocsr()
         helpers.assert_csr_bitwise(_csr_np(got), oracle.transpose_compressed(M.indptr, M.indices, M.data, m), f"csc->csr {path} {m}x{n}")
+    # and csr_matrix.sum_duplicates (rows of up to 300 / 3000 entries: in-row sort and radix fallback)
+    rng = np.random.default_rng(4)
+    for rows, n, top in [(500, 64, 300), (40, 5000, 3000)]:
+        lens = rng.integers(0, top, rows)
+        indptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+        indices = rng.integers(0, n, indptr[-1]).astype(np.int32)
+        data = rng.standard_normal(indptr[-1]).astype(np.float32)
+        g = spmm_b200.csr_matrix((data, indices, indptr), shape=(rows, n))
+        g.sum_duplicates()
+        helpers.assert_csr_bitwise(_csr_np(g), oracle.csr_sum_duplicates((indptr, indices, data), (rows, n)), f"csr dups {path} {rows}x{n}")
 
 
 def test_coo_long_duplicate_run_and_determinism():
