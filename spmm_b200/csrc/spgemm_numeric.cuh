@@ -1031,6 +1031,7 @@ k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ti
   __shared__ __align__(8) unsigned long long s_turn[NW];  // hand-off barriers of the window path
   // the window path reuses the staging array: prefix of the segment lengths, start - prefix, A value
   static_assert(sizeof(s_seg) >= (2 * NT + 2) * sizeof(int) + 8 + NT * sizeof(T), "staging alias");
+  static_assert(sizeof(s_seg) >= NW * 64 * sizeof(int), "sweep alias");
   int *f_pre = reinterpret_cast<int *>(s_seg);
   int *f_sbase = f_pre + NT + 1;
   T *f_a = reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(s_seg) + (((2 * NT + 1) * sizeof(int) + 7) & ~size_t(7)));
@@ -1213,41 +1214,74 @@ k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ti
       }
       const int tot0 = __shfl_sync(FULL, inc0, 31), tot = tot0 + __shfl_sync(FULL, inc1, 31);
       const int ex0 = inc0 - g0, ex1 = tot0 + inc1 - g1;  // exclusive prefix of groups lane and lane + 32
-      for (int g = w; g < ngrp; g += NW) {
-        const int gbase = __shfl_sync(FULL, g < 32 ? ex0 : ex1, g & 31);
-        const int gcnt = __shfl_sync(FULL, g < 32 ? g0 : g1, g & 31);
-        if (gcnt == 0) continue;  // warp-uniform
-        const int i = (g << 5) + lane;
-        unsigned word = i < nwords ? bm[i] : 0u;
-        const int c = __popc(word);
-        int inc = c;
+      // Emit.  Every warp takes a contiguous run of groups holding about tot / NW entries (boundaries from the
+      // prefix: the hot low columns no longer unbalance contiguous ranges) and walks it with a running output
+      // offset.  Non-empty bitmap words are first gathered, 32 at a time, into the warp's pending list, and only
+      // then handed one per lane: in the sparse stretches of a power-law row most words of a group are empty and
+      // a per-group scan + walk spent ~3 warp instructions per entry on them.
+      {
+        // groups are assigned by the rank of their first entry: run w = the groups whose exclusive prefix lies in
+        // [tot w / NW, tot (w + 1) / NW); groups_below(t) = number of groups with prefix < t = first group at or past t
+        auto groups_below = [&](int t) {
+          const unsigned b0 = __ballot_sync(FULL, lane < ngrp && ex0 < t);
+          const unsigned b1 = __ballot_sync(FULL, lane + 32 < ngrp && ex1 < t);
+          return __popc(b0) + __popc(b1);
+        };
+        const int gbeg = groups_below((int)((long long)tot * w / NW));
+        const int gend = groups_below((int)((long long)tot * (w + 1) / NW));  // trailing empty groups belong to no run
+        int run = out + __shfl_sync(FULL, gbeg < 32 ? ex0 : ex1, gbeg & 31);
+        int *pend = reinterpret_cast<int *>(s_seg) + 64 * w;  // 64 pending words per warp; the staging array is idle during the sweep
+        int npend = 0;
+        const unsigned below = (1u << lane) - 1u;
+        auto flush = [&](int c) {  // the first c (<= 32) pending words, one per lane
+          unsigned word = 0u;
+          int i = 0;
+          if (lane < c) {
+            i = pend[lane];
+            word = bm[i];
+            bm[i] = 0u;
+          }
+          const int cnt = __popc(word);
+          int inc = cnt;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const int u = __shfl_up_sync(FULL, inc, o);
-          if (lane >= o) inc += u;
-        }
-        if (word) bm[i] = 0u;
-        int *cj = Cj + (out + gbase + inc - c);
-        T *cx = Cx + (out + gbase + inc - c);
-        T *ac = acc + (i << 5);
-        const int colbase = c0 + (i << 5);
-        if (alpha == T(1)) {
+          for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(FULL, inc, o);
+            if (lane >= o) inc += u;
+          }
+          int *cj = Cj + (run + inc - cnt);
+          T *cx = Cx + (run + inc - cnt);
+          T *ac = acc + (i << 5);
+          const int colbase = c0 + (i << 5);
           while (word) {
             const int bit = __ffs(word) - 1;
             word &= word - 1;
-            *cx++ = ac[bit];
+            const T v = ac[bit];
+            *cx++ = alpha == T(1) ? v : mul_rn(alpha, v);
             ac[bit] = UNT;
             *cj++ = colbase + bit;
           }
-        } else {
-          while (word) {
-            const int bit = __ffs(word) - 1;
-            word &= word - 1;
-            *cx++ = mul_rn(alpha, ac[bit]);
-            ac[bit] = UNT;
-            *cj++ = colbase + bit;
+          run += __shfl_sync(FULL, inc, 31);
+        };
+        for (int g = gbeg; g < gend; ++g) {
+          const int i = (g << 5) + lane;
+          const unsigned word = i < nwords ? bm[i] : 0u;
+          const unsigned nz = __ballot_sync(FULL, word != 0u);
+          if (nz == 0u) continue;  // warp-uniform
+          if (word) pend[npend + __popc(nz & below)] = i;
+          npend += __popc(nz);
+          __syncwarp();
+          if (npend >= 32) {
+            flush(32);
+            __syncwarp();
+            const int rest = npend - 32;
+            const int moved = lane < rest ? pend[32 + lane] : 0;
+            __syncwarp();
+            if (lane < rest) pend[lane] = moved;
+            npend = rest;
+            __syncwarp();
           }
         }
+        if (npend > 0) flush(npend);
       }
       out += tot;
       __syncthreads();
