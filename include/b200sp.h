@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define B200SP_VERSION 100 /* 0.1.0 */
+#define B200SP_VERSION 200 /* 0.2.0: round 2 (single-pass SpGEMM, packed B, bucket conversions, noalloc SpMV) */
 
 typedef struct b200sp_context *b200sp_handle_t;
 

@@ -33,7 +33,7 @@ def test_header_symbols_exported_and_bound():
         assert hasattr(lib, n), f"{n} declared in b200sp.h but not exported by libb200sp.so"
         assert n in bound, f"{n} declared in b200sp.h but not bound in spmm_b200/_lib.py"
     assert bound <= set(names), f"bound but undeclared: {bound - set(names)}"
-    assert lib.b200sp_version() == 100
+    assert lib.b200sp_version() == 200
     assert lib.b200sp_status_string(-3) == b"out of memory"
 
 
