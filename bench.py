@@ -430,6 +430,10 @@ def run_ours(args):
             extra["d2h_probe"] = d2h_probe(torch, dist, dev, world, rank, multi)
             extra["spmv_c2_multi"] = spmv_multi(torch, dist, dev, world, rank, spmm_b200, multi, flush)
         if not args.no_c5:
+            if args.c5_ab:  # A/B inside one run: the same job with the hub rows not split over CTAs
+                os.environ["B200SP_NO_HUB_SPLIT"] = "1"
+                extra["c5_strong_no_hub_split"] = c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, args.c5_scale)
+                os.environ.pop("B200SP_NO_HUB_SPLIT", None)
             extra["c5_strong"] = c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, args.c5_scale)
     if rank != 0:
         if world > 1:
@@ -984,6 +988,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extra", action="store_true")
     ap.add_argument("--no-c5", action="store_true")
+    ap.add_argument("--c5-ab", action="store_true", help="also run extra.c5_strong with B200SP_NO_HUB_SPLIT=1 (A/B in one run)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

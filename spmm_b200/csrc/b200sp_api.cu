@@ -68,6 +68,7 @@ struct Plan {
   int sym_count[MAX_BINS]{}, num_count[MAX_BINS]{};
   int *rows_sym = nullptr, *rows_num = nullptr;  // device, inside ws
   int64_t num_products = 0, nnzC = 0, max_row_products = 0;
+  bool heavy_ordered = false;  // the last numeric bin's row list is ordered by decreasing work and its bucket histogram is in ctr->sym_count
   bool stage1 = false;      // row products / bound / symbolic bins of the current arguments are in ws (estimate ran)
   bool single_pass = false; // the estimate chose the single-pass kernel
   int64_t nnz_bound = 0;    // sum_i min(products_i, n)
@@ -589,8 +590,29 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         int per_sm = 1;
         CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt, smem));
         const int grid = std::max(1, std::min(cnt, h->num_sms * std::max(1, per_sm)));
-        CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, sizeof(int), st));  // rows are handed out by ticket
-        kern<<<grid, nt, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, flat_below);
+        CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, 2 * sizeof(int), st));  // rows are handed out by ticket ([1]: the hub pre-pass)
+        const int *hub_hist = nullptr, *hub_offs = nullptr;
+        int grid_main = grid;
+        // ... when the largest row alone exceeds a CTA's fair share of the products, i.e. is the critical path (the
+        // pre-pass walks the hub rows' structure once more: measured at N = 1 it costs 13 % / 4 % of the numeric pass
+        // at R-MAT scale 16 / 18, where no row is that large, and gains 1 % at scale 20, where the top rows are)
+        if (p.heavy_ordered && b == p.num_limits.nbins - 1 && !getenv("B200SP_NO_HUB_SPLIT") &&
+            p.max_row_products * (int64_t)(h->num_sms * std::max(1, per_sm)) >= p.num_products) {
+          // the heaviest rows (top two work buckets of the ordered list) are cut into one task per column block
+          Counters *ctr = (Counters *)h->ws.ptr;
+          TRY(ensure(h, h->ws2, (size_t)HUB_MAX * (nblk + 1) * sizeof(int)));
+          int *counts = (int *)h->ws2.ptr;
+          const size_t hsmem = (size_t)(W / 32) * 4;
+          k_hub_counts<<<h->num_sms * 4, 256, hsmem, st>>>(rows, cnt, &ctr->sym_count[0], (int *)h->ws3.ptr + 1, W, nblk, p.Ap, p.Aj,
+                                                          (const int *)h->ws3.ptr + 64, p.Bj, counts);
+          TRY(check_launch(h, "k_hub_counts"));
+          k_hub_offsets<<<(HUB_MAX * 32 + 255) / 256, 256, 0, st>>>(&ctr->sym_count[0], cnt, nblk, counts);
+          TRY(check_launch(h, "k_hub_offsets"));
+          hub_hist = &ctr->sym_count[0];
+          hub_offs = counts;
+          grid_main = h->num_sms * std::max(1, per_sm);  // the task count (rows + hub blocks) is only known on the device
+        }
+        kern<<<grid_main, nt, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, W, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, flat_below, hub_hist, hub_offs);
         return check_launch(h, "k_num_dense_pieces");
       }
       // B not canonical (or absurdly wide): the global-memory kernel takes any input
@@ -715,6 +737,7 @@ int spgemm_stage1(b200sp_context *h, int64_t m, int64_t k, int64_t n, int64_t nn
   p.valid = false;
   p.stage1 = false;
   p.single_pass = false;
+  p.heavy_ordered = false;
   if (m < 0 || k < 0 || n < 0 || nnzA < 0 || nnzB < 0 || m >= INT32_MAX || k >= INT32_MAX || n >= INT32_MAX ||
       nnzA > INT32_MAX || nnzB > INT32_MAX)
     return fail(h, B200SP_ERR_INVALID, "bad shape m=%lld k=%lld n=%lld nnzA=%lld nnzB=%lld", (long long)m,
@@ -878,6 +901,7 @@ int spgemm_stage2(b200sp_context *h, int64_t *nnzC) {
       k_work_order<<<og, 256, 0, st>>>(p.rows_num + off_lb, cnt, rowprod, top_log2, &ctr->sym_count[0], &ctr->sym_cursor[0], p.rows_sym);
       TRY(check_launch(h, "k_work_order"));
       CUDA_TRY(h, cudaMemcpyAsync(p.rows_num + off_lb, p.rows_sym, (size_t)cnt * sizeof(int), cudaMemcpyDeviceToDevice, st));
+      p.heavy_ordered = true;
     }
   }
   *nnzC = p.nnzC;

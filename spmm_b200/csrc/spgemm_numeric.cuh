@@ -1013,6 +1013,82 @@ __device__ __forceinline__ void window_apply(T *__restrict__ acc, unsigned *__re
 // Chunks with fewer products per piece than this take the window path: a window of 32 products
 // costs ~420 cycles of hand-off chain, a piece ~340 cycles of barrier step (measured: R-MAT scale
 // 16/18 unchanged, scale 20 961 -> 827 ms, scale 22 16.3 -> 12.0 s; 64 and above lose at scale 16-18).
+// ---- hub rows split over CTAs ------------------------------------------------------------------
+// The heaviest rows of a power-law matrix are a whole CTA's work for tens of milliseconds (R-MAT scale
+// 20: the top row holds 9.7e6 products, ~60 ms of one CTA), which is what a strong-scaled run on 8 GPUs
+// has left per rank: the longest row, not the work, then sets the time.  The rows within a factor 4 of
+// the largest (the two top buckets of the work-ordered list, at most HUB_MAX rows) are therefore cut
+// into their column blocks - one task per (row, block), taken by different CTAs.  A block's entries
+// start after those of the row's earlier blocks, so their counts are needed first: k_hub_counts
+// walks the structure of every (hub row, block) once (bitmap in shared memory, ~5 % of the products),
+// k_hub_offsets turns the counts of a row into offsets.
+constexpr int HUB_MAX = 256;
+
+__device__ __forceinline__ int hub_rows(const int *__restrict__ hist, int nrows) {
+  return min(min(hist[15] + hist[14], HUB_MAX), nrows);
+}
+
+__global__ void __launch_bounds__(256)
+k_hub_counts(const int *__restrict__ rows, int nrows, const int *__restrict__ hist, int *__restrict__ ticket, int W, int nblk,
+             const int *__restrict__ Ap, const int *__restrict__ Aj, const int *__restrict__ bounds,
+             const int *__restrict__ Bj, int *__restrict__ counts /* [HUB_MAX][nblk + 1] */) {
+  extern __shared__ unsigned hub_bm[];  // W / 32 words
+  __shared__ int s_t, s_cnt;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, nw = blockDim.x >> 5;
+  const int H = hub_rows(hist, nrows), ntasks = H * nblk, nwords = W >> 5;
+  for (;;) {
+    if (tid == 0) {
+      s_t = atomicAdd(ticket, 1);
+      s_cnt = 0;
+    }
+    for (int i = tid; i < nwords; i += blockDim.x) hub_bm[i] = 0u;
+    __syncthreads();
+    const int t = s_t;
+    if (t >= ntasks) break;
+    const int hrow = t / nblk, b = t - hrow * nblk, row = rows[hrow], c0 = b * W;
+    const int a_end = __ldg(Ap + row + 1);
+    for (int e = __ldg(Ap + row) + w; e < a_end; e += nw) {
+      const int *bd = bounds + (size_t)__ldg(Aj + e) * (nblk + 1) + b;
+      const int se = __ldg(bd + 1);
+      for (int u = __ldg(bd) + lane; u < se; u += 32) {
+        const int lc = __ldg(Bj + u) - c0;
+        atomicOr(hub_bm + (lc >> 5), 1u << (lc & 31));
+      }
+    }
+    __syncthreads();
+    int c = 0;
+    for (int i = tid; i < nwords; i += blockDim.x) c += __popc(hub_bm[i]);
+    c = warp_sum(c);
+    if (lane == 0 && c) atomicAdd(&s_cnt, c);
+    __syncthreads();
+    if (tid == 0) counts[hrow * (nblk + 1) + b] = s_cnt;
+    __syncthreads();
+  }
+}
+
+// one warp per hub row: counts[h][0 .. nblk) -> exclusive prefix in place (counts[h][nblk] = the row's total)
+__global__ void __launch_bounds__(256)
+k_hub_offsets(const int *__restrict__ hist, int nrows, int nblk, int *__restrict__ counts) {
+  const int lane = threadIdx.x & 31;
+  const int h = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (h >= hub_rows(hist, nrows)) return;
+  int *c = counts + h * (nblk + 1);
+  int run = 0;
+  for (int b0 = 0; b0 < nblk; b0 += 32) {
+    const int b = b0 + lane;
+    const int v = b < nblk ? c[b] : 0;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(FULL, inc, o);
+      if (lane >= o) inc += u;
+    }
+    if (b < nblk) c[b] = run + inc - v;
+    run += __shfl_sync(FULL, inc, 31);
+  }
+  if (lane == 0) c[nblk] = run;
+}
+
 constexpr int PIECES_FLAT_BELOW = 32;
 
 template <typename T, int NT, int WPT>
@@ -1020,7 +1096,8 @@ __global__ void __launch_bounds__(NT, 1)
 k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ticket, int n, int W, int nblk,
                    const int *__restrict__ Ap, const int *__restrict__ Aj, const T *__restrict__ Ax,
                    const int *__restrict__ bounds, const int *__restrict__ Bj, const T *__restrict__ Bx,
-                   int nnzB, const int *__restrict__ Cp, int *__restrict__ Cj, T *__restrict__ Cx, T alpha, int flat_below) {
+                   int nnzB, const int *__restrict__ Cp, int *__restrict__ Cj, T *__restrict__ Cx, T alpha, int flat_below,
+                   const int *__restrict__ hub_hist, const int *__restrict__ hub_offs) {
   constexpr int NW = NT / 32, CAP = 2 * NT;
   extern __shared__ __align__(16) unsigned char smem_raw[];  // W accumulators, then W/32 bitmap words
   __shared__ DenseSeg<T> s_seg[CAP + BLOCKED_PAD];
@@ -1049,15 +1126,29 @@ k_num_dense_pieces(const int *__restrict__ rows, int nrows, int *__restrict__ ti
   __syncthreads();
   // rows are handed out by a global ticket: heavy rows differ 1000-fold in work, a fixed
   // round-robin deal left the slowest CTA 1.2-1.35x behind the mean (R-MAT scale 16-18)
+  // hub_hist != nullptr: the first H rows of the (work-ordered) list are hub rows, cut into H * nblk tasks of one
+  // column block each, whose offsets inside the row are in hub_offs (k_hub_counts / k_hub_offsets); tickets
+  // [0, H * nblk) are those tasks (row-major, heaviest rows first), the later ones the remaining rows
+  const int H = hub_hist ? hub_rows(hub_hist, nrows) : 0;
+  const int hub_tasks = H * nblk;
   while (true) {
     if (tid == 0) s_ticket = atomicAdd(ticket, 1);
     __syncthreads();
-    const int ridx = s_ticket;  // the next write is behind the barriers of this row's blocks
+    const int tk = s_ticket;  // the next write is behind the barriers of this row's blocks
+    int ridx, cb_lo = 0, cb_hi = nblk, hub_off = 0;
+    if (tk < hub_tasks) {
+      ridx = tk / nblk;
+      cb_lo = tk - ridx * nblk;
+      cb_hi = cb_lo + 1;
+      hub_off = __ldg(hub_offs + ridx * (nblk + 1) + cb_lo);
+    } else {
+      ridx = tk - hub_tasks + H;
+    }
     if (ridx >= nrows) break;
     const int row = rows[ridx];
     const int a_begin = __ldg(Ap + row), a_end = __ldg(Ap + row + 1);
-    int out = __ldg(Cp + row);
-    for (int cb = 0; cb < nblk; ++cb) {
+    int out = __ldg(Cp + row) + hub_off;
+    for (int cb = cb_lo; cb < cb_hi; ++cb) {
       const int c0 = cb * W;
       for (int base = a_begin; base < a_end; base += NT) {
         // ---- stage: thread t takes A nonzero base+t; the segment of its B row inside the block is
