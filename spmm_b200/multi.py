@@ -199,18 +199,22 @@ def unpack_csr(buf, nrows, nnz, val_dtype):
     return (buf[:o1].view(torch.int32), buf[o1:o2].view(torch.int32), buf[o2:].view(val_dtype))
 
 
-def broadcast_csr(B, src=0, device=None):
+def broadcast_csr(B, src=0, device=None, meta=None):
     """Broadcast a CSR (tuple of int32 / int32 / fp32|fp64 tensors on `src`, None elsewhere).
     Metadata (rows, nnz, dtype code) goes first as 3 int64, then the packed arrays in one
-    dist.broadcast."""
+    dist.broadcast.  `meta` = (rows, nnz, dtype code) when every rank already knows them (an SPMD
+    job that multiplies by the same B again): the metadata exchange - a second collective and a
+    host synchronisation in front of the payload - is skipped."""
     rank = dist.get_rank()
     device = device or (B[0].device if B is not None else torch.device("cpu"))
-    meta = torch.zeros(3, dtype=torch.int64, device=device)
-    if rank == src:
-        p, j, x = B
-        meta[0], meta[1], meta[2] = p.numel() - 1, j.numel(), 1 if x.dtype == torch.float64 else 0
-    dist.broadcast(meta, src=src)
-    nrows, nnz, code = (int(v) for v in meta.tolist())
+    if meta is None:
+        mt = torch.zeros(3, dtype=torch.int64, device=device)
+        if rank == src:
+            p, j, x = B
+            mt[0], mt[1], mt[2] = p.numel() - 1, j.numel(), 1 if x.dtype == torch.float64 else 0
+        dist.broadcast(mt, src=src)
+        meta = mt.tolist()
+    nrows, nnz, code = (int(v) for v in meta)
     vdt = torch.float64 if code else torch.float32
     nbytes = (nrows + 1) * 4 + nnz * 4 + nnz * (8 if code else 4)
     if rank == src:
