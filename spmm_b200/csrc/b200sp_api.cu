@@ -653,7 +653,7 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
       TRY(ensure(h, h->ws2, (size_t)ntasks * sizeof(unsigned)));  // per-task status words of the look-back
       CUDA_TRY(h, cudaMemsetAsync(h->ws2.ptr, 0, (size_t)ntasks * sizeof(unsigned), st));
       CUDA_TRY(h, cudaMemsetAsync(h->ws3.ptr, 0, sizeof(int), st));  // the task ticket
-      k_num_warp_blocks<T><<<grid, WB_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, WW, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, getenv("B200SP_WB_NOWAIT") ? nullptr : (unsigned *)h->ws2.ptr);
+      k_num_warp_blocks<T><<<grid, WB_NT, smem, st>>>(rows, cnt, (int *)h->ws3.ptr, p.n, WW, nblk, p.Ap, p.Aj, Ax, (const int *)h->ws3.ptr + 64, p.Bj, Bx, (int)p.nnzB, p.Cp, Cj, Cx, alpha, (unsigned *)h->ws2.ptr);
       return check_launch(h, "k_num_warp_blocks");
     }
     case NUM_RANK: {

@@ -209,7 +209,7 @@ k_num_warp_blocks(const int *__restrict__ rows, int nrows, int *__restrict__ tic
       int mine_cnt = 0;
       for (int i = lane; i < nw; i += 32) mine_cnt += __popc(bm[i]);
       const int own = warp_sum(mine_cnt);
-      const int excl = status ? wb_lookback(status, (long long)ridx * nblk + b, b, own, lane) : 0;  // status == nullptr: timing experiment only (wrong offsets)
+      const int excl = wb_lookback(status, (long long)ridx * nblk + b, b, own, lane);
       if (own == 0) continue;  // warp-uniform
       int out = __ldg(Cp + row) + excl;
       for (int i0 = 0; i0 < nw; i0 += 32) {

@@ -48,10 +48,8 @@ CONFIGS = {
     "warp_ww1280": {"B200SP_HEAVY": "warp", "B200SP_WARP_WW": "1280"},
     "warp_ww5120": {"B200SP_HEAVY": "warp", "B200SP_WARP_WW": "5120"},
     "warp_t512": {"B200SP_HEAVY": "warp", "B200SP_HEAVY_MIN": "512"},
-    "warp_nowait": {"B200SP_HEAVY": "warp", "B200SP_WB_NOWAIT": "1"},  # timing experiment: offsets wrong, checksums fail
-    "warp_nowait_ww5120": {"B200SP_HEAVY": "warp", "B200SP_WB_NOWAIT": "1", "B200SP_WARP_WW": "5120"},
 }
-KEYS = ("B200SP_WB_NOWAIT", "B200SP_WARP_WW", "B200SP_BLOCKED_NT", "B200SP_BLOCKED_KB", "B200SP_HEAVY", "B200SP_RANK_ACC_KB", "B200SP_HEAVY_MIN", "B200SP_HEAVY_DENSE_DIV", "B200SP_WINDOW_TURN", "B200SP_FLAT_BELOW")
+KEYS = ("B200SP_WARP_WW", "B200SP_BLOCKED_NT", "B200SP_BLOCKED_KB", "B200SP_HEAVY", "B200SP_RANK_ACC_KB", "B200SP_HEAVY_MIN", "B200SP_HEAVY_DENSE_DIV", "B200SP_WINDOW_TURN", "B200SP_FLAT_BELOW")
 
 
 def run_once(A, b, rp, dev):
