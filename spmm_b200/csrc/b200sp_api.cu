@@ -510,6 +510,9 @@ int pack_b(b200sp_context *h, const T *Bx, const PBEnt<T> **pb, int *pb_last) {
   return B200SP_OK;
 }
 
+// prefetch depth of k_num_dense_cta: 12 when the accumulator alone limits the SM to three CTAs (see DENSE_DEPTH_MAX)
+inline bool dense_deep(size_t acc_bytes) { return acc_bytes * 4 > SMEM_MAX - 4 * 6144; }
+
 template <typename T>
 int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alpha, const T *Ax,
                        const T *Bx, int *Cj, T *Cx) {
@@ -548,8 +551,13 @@ int launch_numeric_bin(b200sp_context *h, int b, const int *rows, int cnt, T alp
         const PBEnt<T> *pb = nullptr;
         int pb_last = 0;
         TRY(pack_b<T>(h, Bx, &pb, &pb_last));
-        TRY(set_smem(h, k_num_dense_cta<T, false>, smem));
-        k_num_dense_cta<T, false><<<persistent_grid(h, cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, pb, pb_last, p.Cp, Cj, Cx, alpha, SinglePassArgs{});
+        if (dense_deep(smem)) {
+          TRY(set_smem(h, k_num_dense_cta<T, false, 12>, smem));
+          k_num_dense_cta<T, false, 12><<<persistent_grid(h, cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, pb, pb_last, p.Cp, Cj, Cx, alpha, SinglePassArgs{});
+        } else {
+          TRY(set_smem(h, k_num_dense_cta<T, false, 8>, smem));
+          k_num_dense_cta<T, false, 8><<<persistent_grid(h, cnt, smem + 7424), nt, smem, st>>>(rows, cnt, p.n, p.Ap, p.Aj, Ax, p.Bp, pb, pb_last, p.Cp, Cj, Cx, alpha, SinglePassArgs{});
+        }
         return check_launch(h, "k_num_dense_cta");
       }
       // fp64 with n between the fp32 and fp64 budgets: column blocks
@@ -998,9 +1006,14 @@ int run_single_pass(b200sp_context *h, const void *alpha, const void *Ax, const 
   // query cost ~10 us of host time between the estimate and the launch: done once per (type, shape) and handle
   const int key_t = (int)sizeof(T);
   if (h->sp_key_t != key_t || h->sp_key_nt != nt || h->sp_key_smem != smem) {
-    TRY(set_smem(h, k_num_dense_cta<T, true>, smem));
     int per_sm = 0;
-    CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_dense_cta<T, true>, nt, smem));
+    if (dense_deep(smem)) {
+      TRY(set_smem(h, k_num_dense_cta<T, true, 12>, smem));
+      CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_dense_cta<T, true, 12>, nt, smem));
+    } else {
+      TRY(set_smem(h, k_num_dense_cta<T, true, 8>, smem));
+      CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_num_dense_cta<T, true, 8>, nt, smem));
+    }
     if (per_sm < 1) return fail(h, B200SP_ERR_CUDA, "k_num_dense_cta<single pass> does not fit an SM");
     h->sp_key_t = key_t; h->sp_key_nt = nt; h->sp_key_smem = smem; h->sp_per_sm = per_sm;
   }
@@ -1011,8 +1024,12 @@ int run_single_pass(b200sp_context *h, const void *alpha, const void *Ax, const 
   const PBEnt<T> *pb = nullptr;
   int pb_last = 0;
   TRY(pack_b<T>(h, (const T *)Bx, &pb, &pb_last));
-  k_num_dense_cta<T, true><<<grid, nt, smem, st>>>(nullptr, p.m, p.n, p.Ap, p.Aj, (const T *)Ax, p.Bp, pb, pb_last, nullptr, Cj,
-                                                  (T *)Cx, a, sp);
+  if (dense_deep(smem))
+    k_num_dense_cta<T, true, 12><<<grid, nt, smem, st>>>(nullptr, p.m, p.n, p.Ap, p.Aj, (const T *)Ax, p.Bp, pb, pb_last, nullptr, Cj,
+                                                        (T *)Cx, a, sp);
+  else
+    k_num_dense_cta<T, true, 8><<<grid, nt, smem, st>>>(nullptr, p.m, p.n, p.Ap, p.Aj, (const T *)Ax, p.Bp, pb, pb_last, nullptr, Cj,
+                                                       (T *)Cx, a, sp);
   return check_launch(h, "k_num_dense_cta<single pass>");
 }
 

@@ -396,8 +396,12 @@ template <> struct NegZero<double> {
 };
 
 constexpr int DENSE_MAX_NT = 192;  // 3 CTAs of 6 warps: at most 5 warps per scheduler partition, 96 registers each
-constexpr int DENSE_DEPTH = 8;      // B-row pieces whose loads are in flight ahead of the one being applied
-constexpr int DENSE_PAD = 2 * DENSE_DEPTH;  // zero-length staging entries after the last piece: the prefetch reads up to cnt + 2 D - 1
+// B-row pieces whose loads are in flight ahead of the one being applied: DEPTH template parameter of the kernel, 8 or 12.
+// Twelve when shared memory already limits the SM to three CTAs (n > 12 K columns in fp32: the extra registers are
+// free), eight when more CTAs fit.  One call, variants built from the same sources (tools/gpu_r2_ac.sh): C3 d = 1e-2
+// kernel 1.101 -> 1.057 ms with 12, C4 8192^2 d = 3e-2 0.915 -> 0.959 ms (four CTAs of 79 registers became three).
+constexpr int DENSE_DEPTH_MAX = 12;
+constexpr int DENSE_PAD = 2 * DENSE_DEPTH_MAX;  // zero-length staging entries after the last piece: the prefetch reads up to cnt + 2 D - 1
 constexpr int DENSE_CAP = 2 * DENSE_MAX_NT;  // staged pieces per round
 
 // Global loads that stay where they are written: the compiler sinks read-only (ld.global.nc)
@@ -743,7 +747,7 @@ __device__ __forceinline__ long long single_pass_lookback(volatile unsigned long
   return excl;
 }
 
-template <typename T, bool SINGLE>
+template <typename T, bool SINGLE, int DEPTH>
 __global__ void __launch_bounds__(DENSE_MAX_NT, 3)
 k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__restrict__ Ap,
                 const int *__restrict__ Aj, const T *__restrict__ Ax, const int *__restrict__ Bp,
@@ -829,7 +833,7 @@ k_num_dense_cta(const int *__restrict__ rows, int nrows, int n, const int *__res
           s_la[cnt + tid] = z;
         }
         __syncthreads();
-        dense_apply_staged<T, DENSE_DEPTH>(acc, s_start, s_la, cnt, tid, pb, pb_last);
+        dense_apply_staged<T, DEPTH>(acc, s_start, s_la, cnt, tid, pb, pb_last);
         __syncthreads();
       }
       if (total == 0) __syncthreads();  // s_scan is rewritten by the next chunk

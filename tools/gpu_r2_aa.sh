@@ -1,5 +1,5 @@
 #!/bin/bash
-# round 2, GPU call AA: final build of round 2 (v21): whole suite, smoke, bench + reference arm, launch list, ncu --set full
+# round 2, GPU call AA: final build of round 2 (v22: prefetch depth 12 where three CTAs fit, hub split): whole suite, smoke, bench + reference arm, launch list, ncu --set full
 mkdir -p gpurun_out
 ( time timeout 1800 python -m pytest tests -m gpu -x -q ) > gpurun_out/aa_pytest.txt 2>&1
 echo "pytest rc=$?" >> gpurun_out/aa_pytest.txt
