@@ -431,10 +431,14 @@ def run_ours(args):
             extra["d2h_probe"] = d2h_probe(torch, dist, dev, world, rank, multi)
             extra["spmv_c2_multi"] = spmv_multi(torch, dist, dev, world, rank, spmm_b200, multi, flush)
         if not args.no_c5:
-            if args.c5_ab:  # A/B inside one run: the same job with the hub rows not split over CTAs
+            if args.c5_ab:  # A/B inside one run: the same job without one of its two scheduling measures
                 os.environ["B200SP_NO_HUB_SPLIT"] = "1"
                 extra["c5_strong_no_hub_split"] = c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, args.c5_scale)
                 os.environ.pop("B200SP_NO_HUB_SPLIT", None)
+                if world > 1 and not args.c5_dynamic:
+                    args.c5_dynamic = True
+                    extra["c5_strong_dynamic_queue"] = c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, args.c5_scale)
+                    args.c5_dynamic = False
             extra["c5_strong"] = c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, args.c5_scale)
     if rank != 0:
         if world > 1:
@@ -612,6 +616,17 @@ def c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, scale
     total_products = int(rp.sum())
     subs_all = multi.plan_sub_panels(rp, n, world, 4 if world > 1 else 1)
     mine = subs_all[rank]
+    # --c5-dynamic: the panels are not dealt in advance but drawn from a queue shared by the ranks of the node, heaviest
+    # first (8 per rank on average).  Measured in one run on 8 B200 (profiles/r02_bench_n8_v23_queue_ab.json): the rank
+    # times close up (92 - 105 ms against 68 - 92 ms) but around a higher mean (98 against 79 ms) - 64 panels cost more
+    # than 32 - so the job takes 105 ms instead of 92: the fixed block-cyclic deal stays the default.  (2 GPUs: 292 ms
+    # against 313.)
+    dynamic = world > 1 and args.c5_dynamic
+    queue, panels = None, None
+    if dynamic:
+        panels = multi.work_ordered_panels(rp, n, 8 * world)
+        queue = multi.PanelQueue()
+    drawn = []
     src = None
     if world > 1 and rank == 0:
         src = tuple(torch.from_numpy(x).to(dev) for x in multi.cast_csr_host(A))
@@ -631,7 +646,20 @@ def c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, scale
         ev[1].record()
         chk = torch.zeros(4, dtype=torch.int64, device=dev)
         ms_num, cev = 0.0, []
-        for p0, p1 in mine:
+        drawn.clear()
+
+        def my_panels():
+            if not dynamic:
+                yield from mine
+                return
+            while True:
+                i = queue.next()
+                if i >= len(panels):
+                    return
+                drawn.append(panels[i])
+                yield panels[i]
+
+        for p0, p1 in my_panels():
             pp, pj, px = multi.slice_rows(*At, p0, p1)
             a = spmm_b200.csr_matrix((np.ascontiguousarray(px), np.ascontiguousarray(pj), pp), shape=(p1 - p0, n))
             a._canonical = True
@@ -647,16 +675,23 @@ def c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, scale
         ms_chk = sum(x.elapsed_time(y) for x, y in cev)
         return chk, ev[0].elapsed_time(ev[2]) - ms_chk, ev[0].elapsed_time(ev[1]), ms_num
 
+    if dynamic:
+        queue.reset()
     step()
     if world > 1:
         dist.barrier()
     st0 = _lib.stats(dev.index)
     runs = []
     for _ in range(2):
-        if world > 1:
+        if dynamic:
+            queue.reset()  # collective, ends with a barrier
+        elif world > 1:
             dist.barrier()
         runs.append(step())
     st1 = _lib.stats(dev.index)
+    if dynamic:
+        mine = sorted(drawn)  # what this rank processed in the last run (for the per-rank figures and the row check below)
+        queue.close()
     chk = runs[-1][0].clone()
     mine_ms = float(np.mean([r[1] for r in runs]))
     tt = torch.tensor([mine_ms, float(np.mean([r[2] for r in runs])), float(np.mean([r[3] for r in runs]))], dtype=torch.float64, device=dev)
@@ -699,7 +734,10 @@ def c5_strong(args, torch, dist, dev, world, rank, spmm_b200, multi, _lib, scale
             "ms": ms, "gflops": 2.0 * total_products / ms / 1e6, "products": total_products, "nnzC": got["nnz"],
             "per_rank_ms": {"min": float(per_rank[:, 0].min()), "mean": float(per_rank[:, 0].mean()), "max": ms},
             "ms_broadcast_B": float(per_rank[:, 1].max()) if world > 1 else None,
-            "sub_panels_per_rank": [len(s_) for s_ in subs_all], "gpu_launches_rank0": int(st1.kernel_launches - st0.kernel_launches),
+            "sub_panels_per_rank": ([len(s_) for s_ in subs_all] if not dynamic else None),
+            "panel_schedule": (f"dynamic: {len(panels)} product-balanced panels drawn heaviest-first from a queue shared by the ranks (multi.PanelQueue); rank 0 processed {len(mine)}"
+                               if dynamic else "static: block-cyclic deal of 4 panels per rank (multi.plan_sub_panels)"),
+            "gpu_launches_rank0": int(st1.kernel_launches - st0.kernel_launches),
             "roofline_rank0_numeric": {"achieved_GBps": num_bytes / ms_n / 1e6 if ms_n > 0 else None,
                                        "frac": num_bytes / ms_n / 1e6 / peak if ms_n > 0 else None, "ms_numeric": ms_n},
             "parity": {"checksums": got, "golden": {k: gold[k] for k in got} if gold else None,
@@ -989,7 +1027,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extra", action="store_true")
     ap.add_argument("--no-c5", action="store_true")
-    ap.add_argument("--c5-ab", action="store_true", help="also run extra.c5_strong with B200SP_NO_HUB_SPLIT=1 (A/B in one run)")
+    ap.add_argument("--c5-dynamic", action="store_true", help="extra.c5_strong draws its panels from the shared queue (multi.PanelQueue) instead of the fixed block-cyclic deal")
+    ap.add_argument("--c5-ab", action="store_true", help="also run extra.c5_strong with B200SP_NO_HUB_SPLIT=1 and with --c5-dynamic (A/B in one run)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -222,3 +222,51 @@ def test_spmv_row_panels_world2_gloo():
     assert np.array_equal(res[0][0].view(np.uint32), want.view(np.uint32))   # only rank 0 held x
     (a0, a1, n0), (b0, b1, n1) = res[0][1], res[1][1]
     assert a0 == 0 and a1 == b0 and b1 == 301 and n0 == a1 and n1 == b1 - b0 and 0 < a1 < 301
+
+
+def _queue_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        pq = multi.PanelQueue()
+        got = []
+        for _round in range(2):  # two jobs over the same queue: reset() brings the counter back to 0
+            pq.reset()
+            mine = []
+            while True:
+                i = pq.next()
+                if i >= 37:
+                    break
+                mine.append(i)
+            got.append(mine)
+        pq.close()
+        q.put((rank, got))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_panel_queue_world2_gloo():
+    """The dynamic panel queue of the C5 job: every index is handed out exactly once per round, to whichever
+    rank asks first; work_ordered_panels covers the rows once, heaviest panel first, within the bound."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_queue_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=90) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rnd in range(2):
+        assert sorted(res[0][rnd] + res[1][rnd]) == list(range(37))
+    rng = np.random.default_rng(8)
+    rp = (rng.pareto(1.1, size=700) * 40).astype(np.int64)
+    panels = multi.work_ordered_panels(rp, 64, 12, limit=400)
+    flat = sorted(panels)
+    assert flat[0][0] == 0 and flat[-1][1] == 700 and all(flat[i][1] == flat[i + 1][0] for i in range(len(flat) - 1))
+    w = [int(rp[a:b].sum()) for a, b in panels]
+    assert w == sorted(w, reverse=True)
+    assert all(np.minimum(rp[a:b], 64).sum() <= 400 or b - a == 1 for a, b in panels)
