@@ -38,6 +38,30 @@ def test_row_products_and_balanced_panels():
     assert b == [0, 1, 9]
 
 
+def test_host_row_products_native_contract():
+    """b200sp_host_row_products (host code of libb200sp, no device): int64 sums, empty rows, any index dtype
+    on the Python side, and a clear error for a column index outside B's rows or a malformed indptr."""
+    from oracle import oracle
+    rng = np.random.default_rng(12)
+    A = sp.random(3000, 800, density=0.02, format="csr", dtype=np.float32, random_state=rng)
+    B = sp.random(800, 500, density=0.3, format="csr", dtype=np.float32, random_state=rng)
+    want = oracle.row_products(A.indptr, A.indices, B.indptr)
+    got = multi.row_products(A.indptr.astype(np.int64), A.indices.astype(np.int64), B.indptr.astype(np.int64))
+    assert got.dtype == np.int64 and np.array_equal(got, want)
+    assert np.array_equal(got, np.asarray(A.astype(bool).astype(np.int64) @ np.diff(B.indptr)).ravel())
+    assert multi.row_products(np.zeros(1, np.int32), np.zeros(0, np.int32), B.indptr).size == 0
+    bad = A.indices.copy()
+    bad[5] = 800
+    with pytest.raises(ValueError):
+        multi.row_products(A.indptr, bad, B.indptr)
+    with pytest.raises(ValueError):
+        multi.row_products(np.array([0, 3, 2], np.int32), np.array([0, 1, 2], np.int32), B.indptr)
+    # a sum beyond int32: 70 000 references to a row of 40 000 entries
+    Bp = np.array([0, 40000], np.int32)
+    Ap = np.array([0, 70000], np.int32)
+    assert multi.row_products(Ap, np.zeros(70000, np.int32), Bp).tolist() == [70000 * 40000]
+
+
 def test_cast_csr_host_int64_indices():
     """SciPy hands out int64 index arrays for COO-built matrices: the packed broadcast is sized
     for int32, so the host cast must normalise them (and refuse what does not fit)."""
